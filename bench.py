@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 path tracer (BASELINE.json metric: Mrays/s at 4K/64 spp
+on the synthetic 10M-sphere scene, plus LBVH build Mprims/s), one process per GPU.
+
+  python bench.py --gpus 1 --steps 3 --warmup 3                 # our arm (CUDA path through the C ABI)
+  python bench.py --impl reference --gpus 1 --steps 2 --warmup 1  # CPU arm: the oracle port on host cores
+  torchrun --nproc-per-node N ... bench.py --gpus N ...          # spp split over N GPUs + NCCL sum
+
+A "step" is one frame of the hot path: per-frame LBVH rebuild (rt_accel_build) + rt_render of all
+samples + rt_resolve.  `value` times it with inputs resident in HBM; `e2e` times the same frame with
+the particle arrays coming from pinned host memory and the resolved RGBA8 frame going back to the
+host inside the timed region.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))  # oracle_lib: used ONLY by the cpu_baseline / --impl reference legs
+
+B_SEG_EXTRA = 96  # wavefront ray state read + write, SURVEY §8(d)
+
+
+def seg_bytes(n_prims):
+    """Algorithmic bytes per path segment: (ceil(log2 N) + 1) * 64 + 16 + 96."""
+    import math
+    return (math.ceil(math.log2(max(n_prims, 2))) + 1) * 64 + 16 + B_SEG_EXTRA
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n-spheres", type=int, default=10_000_000)
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--depth", type=int, default=5)
+    ap.add_argument("--radius", type=float, default=1.3e-3)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--leaf-max", type=int, default=0)
+    ap.add_argument("--batch-spp", type=int, default=0)
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"C4 synthetic {a.n_spheres} uniform random spheres r={a.radius:g} + 5 box walls (10 tris), "
+            f"{a.width}x{a.height}, {a.spp} spp, depth {a.depth}")
+
+
+def build_scene_host(a, pkg, synth):
+    centers, radii = synth.uniform_spheres(a.n_spheres, a.radius, 0x5EED0001)
+    wv, wn = synth.box_walls(True)
+    ramp = pkg.bake_color_ramp("terrain", a.n_spheres)
+    roughs = np.concatenate([np.float32([[0.73, 0.73, 0.73]]), ramp]).astype(np.float32)
+    metals = np.float32([[0.8, 0.85, 0.88, 0.0]])
+    return dict(centers=centers, radii=radii, wall_v=wv, wall_n=wn, roughs=roughs, metals=metals)
+
+
+def oracle_world(h):
+    n = len(h["radii"])
+    nt = len(h["wall_v"]) // 3
+    kind = np.concatenate([np.arange(n, dtype=np.uint32), np.arange(nt, dtype=np.uint32) | np.uint32(0x80000000)])
+    mat = np.concatenate([np.arange(1, n + 1, dtype=np.uint32), np.zeros(nt, np.uint32)])
+    return dict(kind_index=kind, mat=mat, spheres=np.concatenate([h["centers"], h["radii"][:, None]], 1).astype(np.float32),
+                tri_verts=h["wall_v"].reshape(nt, 9), tri_normals=h["wall_n"].reshape(nt, 9), roughs=h["roughs"], metals=h["metals"])
+
+
+# ---------------------------------------------------------------------------------------------------
+def cpu_sample(a, pkg, host, cam, target_seconds, verbose=False):
+    """Times the CPU oracle (OpenMP over pixel rows, own median-split BVH) on a bounded sample of the
+    same workload: same scene, fewer pixels / samples.  Returns (dict for the JSON line)."""
+    import oracle_lib
+    orc = oracle_lib.load()
+    world = oracle_world(host)
+    t0 = time.perf_counter()
+    acc = orc.accel_create(world)
+    build_s = time.perf_counter() - t0
+    # probe, then size the sample for ~target_seconds.  spp stays high (16) so that the one-off
+    # per-pixel curand_init is amortised as in the real 64-spp workload.
+    spp = min(16, a.spp)
+    w, h = 96, 54
+    t0 = time.perf_counter()
+    r = orc.render_accel(acc, cam, w, h, spp, a.depth, a.seed)
+    dt = max(time.perf_counter() - t0, 1e-3)
+    k = max(1.0, target_seconds / dt) ** 0.5
+    w, h = int(96 * k) // 8 * 8, int(54 * k) // 4 * 4
+    w, h = min(w, a.width), min(h, a.height)
+    t0 = time.perf_counter()
+    r = orc.render_accel(acc, cam, w, h, spp, a.depth, a.seed)
+    dt = time.perf_counter() - t0
+    orc.accel_destroy(acc)
+    return dict(value=r["segments"] / dt / 1e6, unit="Mrays/s", cores=orc.num_threads(), kind="port",
+                sample=f"same scene, {w}x{h}, {spp} spp, depth {a.depth} ({r['segments']} segments in {dt:.1f} s); "
+                       f"oracle BVH build {build_s:.1f} s ({len(world['kind_index']) / build_s / 1e6:.2f} Mprims/s, 1 thread) not in value",
+                build_mprims_s=len(world["kind_index"]) / build_s / 1e6), dt
+
+
+def run_reference(a):
+    """--impl reference: the reference's path on the host cores.  The reference itself cannot run here
+    (closed-source OptiX + graphics stack: unavailable on this box), so this arm times the oracle port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
+    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
+    host = build_scene_host(a, pkg, synth)
+    cam = pkg.camera_configure(**synth.c4_camera())
+    import oracle_lib
+    orc = oracle_lib.load()
+    world = oracle_world(host)
+    tb = time.perf_counter()
+    acc = orc.accel_create(world)
+    build_s = time.perf_counter() - tb
+    # each step = a bounded sample of the frame: the same view at reduced resolution, 16 spp (high
+    # enough that the one-off per-pixel curand_init is amortised as in the 64-spp workload)
+    w, h, spp = 240, 136, min(16, a.spp)
+    times, segs = [], 0
+    for i in range(a.warmup + a.steps):
+        t0 = time.perf_counter()
+        r = orc.render_accel(acc, cam, w, h, spp, a.depth, a.seed + i)
+        dt = time.perf_counter() - t0
+        if i >= a.warmup:
+            times.append(dt)
+            segs += r["segments"]
+    orc.accel_destroy(acc)
+    total = sum(times)
+    val = segs / total / 1e6
+    line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * total / max(1, a.steps), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "reference": "CPU oracle port (OptiX reference unavailable on this box)"},
+            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": orc.num_threads(), "kind": "port",
+                             "sample": f"per step: same scene, {w}x{h}, {spp} spp, depth {a.depth}; BVH build {build_s:.1f} s outside steps"},
+            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
+    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world_size == a.gpus or world_size == 1 and a.gpus == 1, f"launch with torchrun --nproc-per-node {a.gpus}"
+    assert a.spp % world_size == 0, "spp must divide evenly over the ranks"
+    spp_rank = a.spp // world_size
+
+    host = build_scene_host(a, pkg, synth)
+    cam = pkg.camera_configure(**synth.c4_camera())
+    n = a.n_spheres
+    npix = a.width * a.height
+    # pinned host staging (the e2e arm copies from here every step)
+    h_centers = torch.from_numpy(host["centers"]).pin_memory()
+    h_radii = torch.from_numpy(host["radii"]).pin_memory()
+    d_centers = h_centers.to(dev)
+    d_radii = h_radii.to(dev)
+    d_wv = torch.from_numpy(host["wall_v"]).to(dev)
+    d_wn = torch.from_numpy(host["wall_n"]).to(dev)
+    accum = torch.zeros((npix, 4), dtype=torch.float32, device=dev)
+    rgba8 = torch.zeros((npix, 4), dtype=torch.uint8, device=dev)
+    h_rgba8 = torch.zeros((npix, 4), dtype=torch.uint8).pin_memory()
+
+    ctx = pkg.Context(local)
+    sc = pkg.Scene(ctx)
+    if a.leaf_max:
+        sc.set_option("leaf_max", a.leaf_max)
+    if a.batch_spp:
+        sc.set_option("batch_spp", a.batch_spp)
+    sc.set_option("profile", 1)
+    sc.set_materials(host["roughs"].ctypes.data, len(host["roughs"]), host["metals"].ctypes.data, len(host["metals"]))
+    g_s = sc.add_spheres(d_centers.data_ptr(), d_radii.data_ptr(), n)
+    g_w = sc.add_triangles(d_wv.data_ptr(), d_wn.data_ptr(), len(host["wall_v"]) // 3)
+    sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
+    sc.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def frame(step, e2e):
+        if e2e:
+            d_centers.copy_(h_centers, non_blocking=True)
+            d_radii.copy_(h_radii, non_blocking=True)
+        sc.build(stream)
+        sc.render(cam, a.width, a.height, spp_rank, a.depth, a.seed + step, (0.7, 0.8, 0.9), rank * spp_rank, 0,
+                  accum.data_ptr(), None, None, None, stream)
+        if world_size > 1:
+            dist.reduce(accum, 0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
+            if e2e:
+                h_rgba8.copy_(rgba8, non_blocking=True)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e, sampler=None):
+        for i in range(a.warmup):
+            frame(i, e2e)
+        barrier()
+        st0 = sc.stats()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps):
+            frame(a.warmup + i, e2e)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        # segment count and per-launch traversal timings are accumulated on the device / in CUDA
+        # events over the whole region and read once here (no host sync inside the region)
+        st1 = sc.stats()
+        segs = float(st1.segments_total - st0.segments_total)
+        trace_ms = float(st1.trace_ms)
+        build_ms = float(st1.build_ms)
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        sg = torch.tensor([segs], device=dev, dtype=torch.float64)
+        if world_size > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(sg, op=dist.ReduceOp.SUM)
+        return dict(ms=float(t.item()), segs=float(sg.item()), trace_ms=trace_ms, build_ms=build_ms,
+                    launches=int(st1.kernel_launches - st0.kernel_launches), st=st1)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    dv = timed(False, sampler)
+    clocks = sampler.stop() if sampler else None
+    ee = timed(True)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        n_prims = int(dv["st"].n_prims)
+        bseg = seg_bytes(n_prims)
+        st = dv["st"]
+        seg_step = dv["segs"] / world_size / a.steps          # this rank's segments per step
+        trace_step = dv["trace_ms"] / a.steps                   # this rank's traversal-kernel time per step
+        n_launch = max(1, int(st.trace_launches))
+        achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
+        line = {
+            "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "parallelism": f"spp-split x{world_size} + NCCL sum" if world_size > 1 else "single GPU",
+                       "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
+                       "step": "LBVH rebuild + render + resolve", "primary_rays": "traced once per pixel (no jitter in the reference), counted once"},
+            "e2e": {"value": ee["segs"] / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
+                    "h2d_bytes_per_step": int(h_centers.numel() * 4 + h_radii.numel() * 4), "d2h_bytes_per_step": int(h_rgba8.numel())},
+            "gpu_launches": dv["launches"] * world_size,
+            "clocks": clocks,
+            "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
+                      "n_prims": n_prims, "bytes_per_prim": 224,
+                      "hbm_frac": (n_prims * 224 / (dv["build_ms"] * 1e-3) / 1e9 / peak) if dv["build_ms"] > 0 else None},
+            "roofline": {"bound": "hbm", "kernel": "k_primary+k_bounce (BVH traversal)", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "bytes_per_segment": bseg, "segments_per_launch": seg_step * a.steps / n_launch,
+                         "avg_launch_ms": dv["trace_ms"] / n_launch, "trace_launches_per_step": n_launch / a.steps,
+                         "trace_ms_per_step": trace_step, "trace_share_of_step": trace_step / (dv["ms"] / a.steps)},
+            "segments_per_step": seg_step,
+        }
+        if world_size == 1 and not a.no_cpu_baseline:
+            cb, _ = cpu_sample(a, pkg, host, cam, a.cpu_seconds)
+            line["cpu_baseline"] = cb
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line))
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sc.close()
+    ctx.close()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

@@ -1,0 +1,206 @@
+/*
+ * rtb200.h — C ABI of the B200-native path tracer that replaces the OptiX seam of
+ * 3169651074/nvidia-optix-ray-tracer ("RendererOptiX").
+ *
+ * The reference has no plugin/FFI surface; the seam we cut is its OptiX wrapper layer
+ * (include/Global/RendererImpl.cuh:153-253) plus the optixLaunch call sites
+ * (src/Global/RendererTime.cu:484-500, src/Global/RendererMesh.cu:403-419).  Every entry point
+ * below names the reference interface it replaces.  Citations are relative to the reference tree.
+ *
+ * Conventions
+ *   - All functions return an int status (RT_OK = 0).  Nothing ever calls exit(); the reference
+ *     logs and exit(-200/-300) on any failure (src/Global/HostFunctions.cu:30-50).
+ *   - Pointers named dev_* are CUDA device pointers owned by the CALLER and must stay valid until
+ *     the scene is destroyed or the group is replaced (same ownership as the reference's
+ *     dev_centers/dev_radii/dev_normals, src/Global/RendererImpl.cu:508-509,533).  Pointers named
+ *     *_h are host pointers and are copied before the call returns (or stream-ordered if pinned).
+ *   - `stream` is a cudaStream_t passed as void*; NULL = the legacy default stream.  All device
+ *     work is stream-ordered; no entry point performs a device-wide synchronisation except
+ *     rt_get_stats / rt_context_destroy / rt_scene_destroy.
+ *   - A context is bound to one CUDA device.  Calls on different scenes may come from different
+ *     host threads (the reference builds from worker threads on private streams,
+ *     src/Global/RendererMesh.cu:93-100,205-219); calls on the same scene must be serialised.
+ *   - There is NO CPU fallback: with no usable CUDA device rt_context_create fails.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB200_ABI_VERSION 1
+
+/* status codes */
+#define RT_OK 0
+#define RT_ERR_INVALID 1     /* bad argument */
+#define RT_ERR_CUDA 2        /* CUDA runtime error (see rt_last_error) */
+#define RT_ERR_OOM 3         /* device allocation failed */
+#define RT_ERR_UNSUPPORTED 4 /* e.g. non-uniform scale on a sphere instance */
+#define RT_ERR_STATE 5       /* call order violated (render before build, ...) */
+
+/* material types — include/Global/Shader.cuh:16-18 (MaterialType::ROUGH, METAL) */
+#define RT_MAT_ROUGH 0
+#define RT_MAT_METAL 1
+
+/* primitive id written for a primary miss */
+#define RT_MISS_ID 0xFFFFFFFFu
+
+/* rt_frame_params.flags */
+#define RT_FLAG_ACCUMULATE 1u /* add this call's samples to accum_linear instead of overwriting */
+
+/* XORWOW draws reserved per (pixel, sample): stream(p, s) = curand_init(seed, p, (offset+s)*64) */
+#define RT_RNG_SAMPLE_STRIDE 64u
+
+typedef struct rt_context_s *rt_context;
+typedef struct rt_scene_s *rt_scene;
+
+/* Camera basis — RayGenParams.cameraCenter/U/V/W, include/Global/Shader.cuh:27-35.
+ * W = target - center is NOT normalised; U, V are unit (SDL_GraphicsWindow.cu:10-12). */
+typedef struct {
+    float center[3], U[3], V[3], W[3];
+} rt_camera;
+
+/* Per-launch parameters — replaces RayGenParams.width/height, rayTraceDepth
+ * (include/Global/Shader.cuh:8) and MissParams.backgroundColor (Shader.cuh:38-40).
+ * spp / seed / sample_offset are additive: the reference renders 1 spp per frame and seeds
+ * its RNG from clock64() (src/Global/HostFunctions.cu:126). */
+typedef struct {
+    uint32_t width, height;
+    uint32_t spp;           /* samples per pixel rendered by this call */
+    uint32_t max_depth;     /* reference constant: 5 */
+    uint64_t seed;          /* XORWOW seed (subsequence = pixel index y*width+x) */
+    uint32_t sample_offset; /* first sample index of this call (spp split across GPUs / frames) */
+    float background[3];    /* reference: 0.7 0.8 0.9 (src/Global/RendererMesh.cu:260-262) */
+    uint32_t flags;
+} rt_frame_params;
+
+/* Output buffers (device pointers, any may be NULL) — replaces RayGenParams.colorBuffer /
+ * albedoBuffer / normalBuffer (float4[w*h], index y*w+x, shader/Shader.cu:270-272).
+ * accum_linear holds the SUM over this call's samples of linear radiance, w = sample count
+ * (the reference stores one sRGB-encoded sample; encode with rt_resolve). */
+typedef struct {
+    float *accum_linear; /* float4[w*h] */
+    float *albedo;       /* float4[w*h], first-hit albedo, w = 1 on hit */
+    float *normal;       /* float4[w*h], first-hit unit normal, w = 0 */
+    uint32_t *prim_id;   /* u32[w*h], global primitive id of the primary hit or RT_MISS_ID */
+} rt_outputs;
+
+typedef struct {
+    uint64_t n_prims;        /* world-space primitives after instance flattening */
+    uint64_t n_bvh_prims;    /* primitives inside the LBVH */
+    uint64_t n_huge;         /* outlier primitives kept in the linear list */
+    uint64_t n_nodes;        /* internal BVH nodes */
+    uint64_t device_bytes;   /* bytes owned by the scene on the device */
+    float build_ms;          /* device time of the last rt_accel_build (CUDA events) */
+    float render_ms;         /* device time of the last rt_render */
+    uint64_t segments;       /* path segments traversed by the last rt_render */
+    uint64_t kernel_launches;/* kernels launched by this scene since creation */
+    float scene_lo[3], scene_hi[3];
+    float trace_ms;          /* sum of traversal-kernel durations since the previous rt_get_stats (option "profile") */
+    uint32_t trace_launches; /* number of traversal-kernel launches behind trace_ms */
+    uint64_t segments_total; /* path segments traversed by this scene since creation */
+} rt_stats;
+
+/* ---- context: replaces createContext (RendererImpl.cu:6-28) -------------------------------- */
+int rt_context_create(int device, rt_context *out);
+int rt_context_destroy(rt_context ctx);
+/* last error text of the calling thread's most recent failing call on this context */
+const char *rt_last_error(rt_context ctx);
+int rt_abi_version(void);
+
+/* ---- scene assembly: replaces RendererSphere/RendererTriangle/RendererParticle geometry records
+ *      (RendererImpl.cuh:60-90), buildGASForSpheres/Triangles/Particle (RendererImpl.cu:113-172)
+ *      and the OptixInstance fill (RendererTime.cu:116-130, RendererMesh.cu:130-148) ---------- */
+int rt_scene_create(rt_context ctx, rt_scene *out);
+int rt_scene_destroy(rt_scene scene);
+/* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "leaf_max" (1..8
+ * primitives per BVH leaf), "batch_spp" (samples per pixel in flight per wavefront batch). */
+int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
+
+/* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz
+ * (HitGroupParams.rough/metal, Shader.cuh:57-69).  Host or device pointers. */
+int rt_scene_set_materials(rt_scene scene, const float *roughs, size_t n_rough,
+                           const float *metals, size_t n_metal);
+
+/* Geometry groups (object space; the GAS equivalent).  Sphere SoA: float3 centers[n] + float
+ * radii[n] (RendererImpl.cu:124-135).  Triangles: non-indexed float3 vertices[3n] and per-vertex
+ * float3 normals[3n] (RendererImpl.cu:149-159; shader/Shader.cu:140-142). */
+int rt_scene_add_spheres(rt_scene scene, const float *dev_centers, const float *dev_radii,
+                         size_t count, uint32_t *group_out);
+int rt_scene_add_triangles(rt_scene scene, const float *dev_vertices, const float *dev_normals,
+                           size_t count, uint32_t *group_out);
+/* Re-point an existing group at new buffers / a new count (per-frame particle data). */
+int rt_scene_update_group(rt_scene scene, uint32_t group, const float *dev_a, const float *dev_b,
+                          size_t count);
+
+/* Instances, in SBT order (config spheres -> config triangles -> particles).  transform_h is the
+ * row-major 3x4 of OptixInstance.transform; NULL = identity.  Material of primitive k of the
+ * instance = (mat_type, mat_index + k*mat_stride); mat_stride 0 is the reference's one hit record
+ * per instance (RendererImpl.cu:472-575), 1 gives one ramp colour per particle of a big group. */
+int rt_scene_add_instance(rt_scene scene, uint32_t group, const float *transform_h, int mat_type,
+                          uint32_t mat_index, uint32_t mat_stride, uint32_t *instance_out);
+/* Per-frame transform update: replaces memcpy into pin_instances + cudaMemcpy H2D
+ * (RendererTime.cu:436-480).  transforms = float[12*n], host (pinned or pageable) or device. */
+int rt_scene_set_transforms(rt_scene scene, const float *transforms, size_t first_instance,
+                            size_t n, void *stream);
+
+/* ---- accel: replaces buildASImpl + buildIAS + updateIAS (RendererImpl.cu:30-88,174-242) -----
+ * Flattens instances to world space and rebuilds the LBVH (30-bit Morton, radix sort, Karras
+ * hierarchy, bottom-up refit).  Called once per frame. */
+int rt_accel_build(rt_scene scene, void *stream);
+
+/* ---- launch: replaces optixLaunch(pipeline, stream, params, sbt, w, h, 1) and the raygen /
+ *      closest-hit / miss programs of shader/Shader.cu ---------------------------------------- */
+int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *params,
+              const rt_outputs *out, void *stream);
+
+/* ---- display conversion: replaces colorToFloat4 in raygen (Shader.cu:270) and
+ *      convertFloat4ToUchar4Kernel (RendererImpl.cu:672-678).  color = accum.rgb / accum.w,
+ *      clamp, sRGB OETF.  color_srgb float4[n] and/or rgba8 uchar4[n]; either may be NULL. */
+int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *dev_color_srgb,
+               uint8_t *dev_rgba8, void *stream);
+
+int rt_get_stats(rt_scene scene, rt_stats *out); /* synchronises the scene's last stream */
+
+/* Debug/validation export of the built BVH (device -> host copies; synchronises).
+ * nodes: 16 floats per node; slot_geom: 4 floats per slot; slot_prim: u32 per slot. Any NULL. */
+int rt_accel_download(rt_scene scene, float *nodes_h, float *slot_geom_h, uint32_t *slot_prim_h,
+                      uint32_t *sorted_keys_h);
+/* Closest hit for caller-supplied rays through the same traversal kernel (validation):
+ * dev_rays float[8*n] = o.xyz tmin d.xyz tmax; dev_skip u32[n] global prim id or RT_MISS_ID
+ * (may be NULL); outputs dev_t float[n], dev_id u32[n]. */
+int rt_trace_rays(rt_scene scene, const float *dev_rays, const uint32_t *dev_skip, size_t n,
+                  float *dev_t, uint32_t *dev_id, void *stream);
+
+/* ---- host-side maths of the path (pure CPU, no CUDA) ----------------------------------------
+ * rt_camera_configure: SDL_GraphicsWindowConfigureCamera, src/GraphicsAPI/SDL_GraphicsWindow.cu:4-14
+ *   (flip_up != 0 for every API except OpenGL).
+ * rt_construct_transform: MathHelper::constructTransformMatrix, DeviceFunctions.cuh:133-148.
+ * rt_transform_time: per-particle transform of Time mode, src/Global/RendererTime.cu:436-472
+ *   (slerp :297-340, quatToEuler :343-370; reference component order kept).
+ * rt_transform_mesh: Mesh mode, src/Global/RendererMesh.cu:378-391. */
+void rt_camera_configure(const float center[3], const float target[3], const float up[3],
+                         int flip_up, rt_camera *out);
+void rt_construct_transform(const float shift[3], const float rotate_deg[3], const float scale[3],
+                            float out12[12]);
+void rt_transform_time(const float pos[3], const float vel[3], const float quat_cur[4],
+                       const float quat_next[4], float duration, size_t frames_this_file,
+                       size_t frame, const float particle_shift[3], const float particle_scale[3],
+                       float out12[12]);
+void rt_transform_mesh(const float vel[3], float duration, size_t frames_this_file, size_t frame,
+                       const float particle_shift[3], const float particle_scale[3],
+                       float out12[12]);
+
+/* Particle colour ramps -> rough albedo table: resolveColorRampPreset / colorStopsForPreset /
+ * bakeColorRamp, include/Util/ColorRamp.cuh:31-152.  preset is case-insensitive (viridis, plasma,
+ * spectral, terrain, heatmap, grayscale; anything else = viridis).  out_rgb = float[3*count]. */
+int rt_bake_color_ramp(const char *preset, size_t count, float *out_rgb);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */

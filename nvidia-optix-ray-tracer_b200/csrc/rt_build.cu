@@ -1,0 +1,625 @@
+// rt_build.cu — per-frame LBVH build for sm_100a.
+//
+// Replaces the reference's closed-source acceleration-structure path: buildASImpl /
+// buildGASForSpheres / buildGASForTriangles / buildGASForParticle / buildIAS / updateIAS
+// (src/Global/RendererImpl.cu:30-242, all thin wrappers over optixAccelBuild).  Instead of a
+// two-level GAS/IAS that is refitted per frame, instances are flattened to world space and one
+// LBVH is rebuilt from scratch every frame:
+//   flatten+bounds -> decide (huge prims, Morton frame) -> 30-bit Morton keys -> LSD radix sort
+//   (8-bit digits, 4 passes) -> gather to Morton order -> Karras hierarchy -> bottom-up refit.
+// All kernels are HBM-bound streaming passes; algorithmic bytes per primitive are listed in
+// DESIGN.md §5.
+#include <cfloat>
+
+#include "rt_device.cuh"
+
+namespace rtb {
+
+// ------------------------------------------------------------------ small device helpers
+__device__ __forceinline__ uint32_t f2ord(float f) {  // order-preserving float -> uint
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
+}
+
+struct Box3 {
+    F3 lo, hi;
+};
+
+// Unpadded world-space AABB of the primitive whose packed geometry word is g.
+__device__ __forceinline__ Box3 prim_box(float4 g, const float4 *tri_v12) {
+    Box3 b;
+    const uint32_t wb = __float_as_uint(g.w);
+    if (!(wb & 0x80000000u)) {
+        b.lo = f3(g.x - g.w, g.y - g.w, g.z - g.w);
+        b.hi = f3(g.x + g.w, g.y + g.w, g.z + g.w);
+    } else {
+        const uint32_t ti = wb & 0x7FFFFFFFu;
+        const float4 v1 = tri_v12[2 * (size_t)ti];
+        const float4 v2 = tri_v12[2 * (size_t)ti + 1];
+        b.lo = f3(fminf(g.x, fminf(v1.x, v2.x)), fminf(g.y, fminf(v1.y, v2.y)), fminf(g.z, fminf(v1.z, v2.z)));
+        b.hi = f3(fmaxf(g.x, fmaxf(v1.x, v2.x)), fmaxf(g.y, fmaxf(v1.y, v2.y)), fmaxf(g.z, fmaxf(v1.z, v2.z)));
+    }
+    return b;
+}
+// Conservative padding (2^-15 relative per coordinate): together with the 2e-6 widening in the
+// slab test it dominates every rounding error of the box test and the intersectors.
+__device__ __forceinline__ Box3 pad_box(Box3 b) {
+    const float k = 3.0517578125e-5f;
+    const float px = fmaxf(fabsf(b.lo.x), fabsf(b.hi.x)) * k + 1e-30f;
+    const float py = fmaxf(fabsf(b.lo.y), fabsf(b.hi.y)) * k + 1e-30f;
+    const float pz = fmaxf(fabsf(b.lo.z), fabsf(b.hi.z)) * k + 1e-30f;
+    b.lo = f3(b.lo.x - px, b.lo.y - py, b.lo.z - pz);
+    b.hi = f3(b.hi.x + px, b.hi.y + py, b.hi.z + pz);
+    return b;
+}
+__device__ __forceinline__ int extent_bucket(const Box3 &b) {
+    const float e = fmaxf(b.hi.x - b.lo.x, fmaxf(b.hi.y - b.lo.y, b.hi.z - b.lo.z));
+    if (!(e > 0.0f)) return 0;
+    int ex = (int)((__float_as_uint(e) >> 23) & 0xFF) - 127 + 64;
+    return min(max(ex, 0), (int)kExtentBuckets - 1);
+}
+
+// ------------------------------------------------------------------ K1: flatten instances to world space
+// One thread per world primitive.  Spec A.1: p' = ((m0*x + m1*y) + m2*z) + m3.
+__device__ __forceinline__ F3 xform_point(const float *m, F3 p) {
+    return f3(((m[0] * p.x + m[1] * p.y) + m[2] * p.z) + m[3], ((m[4] * p.x + m[5] * p.y) + m[6] * p.z) + m[7],
+              ((m[8] * p.x + m[9] * p.y) + m[10] * p.z) + m[11]);
+}
+__device__ __forceinline__ F3 xform_normal(const float *m, F3 n) {
+    F3 v = f3((m[0] * n.x + m[1] * n.y) + m[2] * n.z, (m[4] * n.x + m[5] * n.y) + m[6] * n.z,
+              (m[8] * n.x + m[9] * n.y) + m[10] * n.z);
+    return normalize3(v);
+}
+
+__global__ void __launch_bounds__(256)
+k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_base, uint32_t n_inst,
+          const GroupDev *__restrict__ groups, uint32_t n_prims, float4 *__restrict__ w_geom,
+          uint32_t *__restrict__ w_mat, float4 *__restrict__ tri_v12, float4 *__restrict__ tri_nrm,
+          uint32_t *__restrict__ bucket_tab) {
+    __shared__ uint32_t s_tab[kExtentBuckets * 8];
+    for (uint32_t i = threadIdx.x; i < kExtentBuckets * 8; i += blockDim.x) {
+        const uint32_t f = i & 7u;
+        s_tab[i] = (f >= 1 && f <= 3) ? 0xFFFFFFFFu : 0u;
+    }
+    __syncthreads();
+
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = gid < n_prims;
+    int bucket = -1;
+    F3 c = f3(0, 0, 0);
+    if (valid) {
+        // last instance whose prim_base <= gid
+        uint32_t lo = 0, hi = n_inst;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(inst_base + mid) <= gid) lo = mid; else hi = mid;
+        }
+        const InstDev *in = insts + lo;
+        const uint32_t k = gid - in->prim_base;
+        const GroupDev g = groups[in->group];
+        const uint32_t mat = in->mat + k * in->mat_stride;
+        float4 wg;
+        Box3 b;
+        if (g.kind == 0) {
+            const F3 oc = f3(g.a[3 * (size_t)k], g.a[3 * (size_t)k + 1], g.a[3 * (size_t)k + 2]);
+            const float rr = g.b[k];
+            if (in->identity) {
+                // identical to xform_point for an identity linear part: ((1*x + 0*y) + 0*z) + t
+                wg = make_float4(oc.x + in->m[3], oc.y + in->m[7], oc.z + in->m[11], rr);
+            } else {
+                const F3 wc = xform_point(in->m, oc);
+                const float s = sqrtf((in->m[0] * in->m[0] + in->m[4] * in->m[4]) + in->m[8] * in->m[8]);
+                wg = make_float4(wc.x, wc.y, wc.z, rr * s);
+            }
+            b = prim_box(wg, nullptr);
+        } else {
+            const uint32_t ti = in->tri_base + k;
+            const float *v = g.a + 9 * (size_t)k;
+            const F3 p0 = xform_point(in->m, f3(v[0], v[1], v[2]));
+            const F3 p1 = xform_point(in->m, f3(v[3], v[4], v[5]));
+            const F3 p2 = xform_point(in->m, f3(v[6], v[7], v[8]));
+            wg = make_float4(p0.x, p0.y, p0.z, __uint_as_float(0x80000000u | ti));
+            tri_v12[2 * (size_t)ti] = make_float4(p1.x, p1.y, p1.z, 0.0f);
+            tri_v12[2 * (size_t)ti + 1] = make_float4(p2.x, p2.y, p2.z, 0.0f);
+            const float *nn = g.b + 9 * (size_t)k;
+            for (int j = 0; j < 3; j++) {
+                F3 n = f3(nn[3 * j], nn[3 * j + 1], nn[3 * j + 2]);
+                if (!in->identity) n = xform_normal(in->m, n);
+                tri_nrm[3 * (size_t)ti + j] = make_float4(n.x, n.y, n.z, 0.0f);
+            }
+            b.lo = f3(fminf(p0.x, fminf(p1.x, p2.x)), fminf(p0.y, fminf(p1.y, p2.y)), fminf(p0.z, fminf(p1.z, p2.z)));
+            b.hi = f3(fmaxf(p0.x, fmaxf(p1.x, p2.x)), fmaxf(p0.y, fmaxf(p1.y, p2.y)), fmaxf(p0.z, fmaxf(p1.z, p2.z)));
+        }
+        w_geom[gid] = wg;
+        w_mat[gid] = mat;
+        bucket = extent_bucket(b);
+        c = f3(0.5f * (b.lo.x + b.hi.x), 0.5f * (b.lo.y + b.hi.y), 0.5f * (b.lo.z + b.hi.z));
+    }
+
+    // per-extent-bucket centroid bounds: warp-aggregate when the whole warp shares a bucket
+    const uint32_t act = __ballot_sync(0xFFFFFFFFu, valid);
+    if (valid) {
+        const uint32_t peers = __match_any_sync(act, bucket);
+        uint32_t kx0 = f2ord(c.x), ky0 = f2ord(c.y), kz0 = f2ord(c.z);
+        uint32_t kx1 = kx0, ky1 = ky0, kz1 = kz0;
+        uint32_t cnt = 1;
+        if (peers == act && act == 0xFFFFFFFFu) {
+            for (int o = 16; o > 0; o >>= 1) {
+                kx0 = min(kx0, __shfl_xor_sync(0xFFFFFFFFu, kx0, o));
+                ky0 = min(ky0, __shfl_xor_sync(0xFFFFFFFFu, ky0, o));
+                kz0 = min(kz0, __shfl_xor_sync(0xFFFFFFFFu, kz0, o));
+                kx1 = max(kx1, __shfl_xor_sync(0xFFFFFFFFu, kx1, o));
+                ky1 = max(ky1, __shfl_xor_sync(0xFFFFFFFFu, ky1, o));
+                kz1 = max(kz1, __shfl_xor_sync(0xFFFFFFFFu, kz1, o));
+            }
+            cnt = 32;
+            if ((threadIdx.x & 31) != 0) cnt = 0;
+        }
+        if (cnt) {
+            uint32_t *t = s_tab + bucket * 8;
+            atomicAdd(t + 0, cnt);
+            atomicMin(t + 1, kx0); atomicMin(t + 2, ky0); atomicMin(t + 3, kz0);
+            atomicMax(t + 4, kx1); atomicMax(t + 5, ky1); atomicMax(t + 6, kz1);
+        }
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < kExtentBuckets; b += blockDim.x) {
+        const uint32_t *t = s_tab + b * 8;
+        if (t[0]) {
+            uint32_t *g = bucket_tab + b * 8;
+            atomicAdd(g + 0, t[0]);
+            atomicMin(g + 1, t[1]); atomicMin(g + 2, t[2]); atomicMin(g + 3, t[3]);
+            atomicMax(g + 4, t[4]); atomicMax(g + 5, t[5]); atomicMax(g + 6, t[6]);
+        }
+    }
+}
+
+__global__ void k_init_buckets(uint32_t *bucket_tab) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < kExtentBuckets * 8) {
+        const uint32_t f = i & 7u;
+        bucket_tab[i] = (f >= 1 && f <= 3) ? 0xFFFFFFFFu : 0u;
+    }
+}
+
+// ------------------------------------------------------------------ K2: decide huge prims + Morton frame
+// Prims whose extent bucket exceeds the median bucket by more than 6 (>= 64x the median extent,
+// e.g. the r=1000 ground sphere of files/config.json:20-30 among r=0.05 particles) are kept out of
+// the tree (at most kMaxHuge of them) and tested linearly by every ray.
+__global__ void k_decide(const uint32_t *__restrict__ bucket_tab, uint32_t n_total, BuildInfo *info) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint32_t run = 0;
+    int median = (int)kExtentBuckets - 1;
+    for (int b = 0; b < (int)kExtentBuckets; b++) {
+        run += bucket_tab[b * 8];
+        if (2 * (uint64_t)run >= (uint64_t)n_total) { median = b; break; }
+    }
+    int huge_bucket = median + 6;
+    uint32_t n_huge = 0;
+    for (int b = huge_bucket + 1; b < (int)kExtentBuckets; b++) n_huge += bucket_tab[b * 8];
+    if (n_huge > kMaxHuge || n_total < 2) {
+        huge_bucket = (int)kExtentBuckets;
+        n_huge = 0;
+    }
+    uint32_t lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0, 0, 0};
+    for (int b = 0; b < (int)kExtentBuckets && b <= huge_bucket; b++) {
+        if (!bucket_tab[b * 8]) continue;
+        for (int a = 0; a < 3; a++) {
+            lo[a] = min(lo[a], bucket_tab[b * 8 + 1 + a]);
+            hi[a] = max(hi[a], bucket_tab[b * 8 + 4 + a]);
+        }
+    }
+    info->n_total = n_total;
+    info->n_huge = n_huge;
+    info->n_bvh = n_total - n_huge;
+    info->huge_bucket = huge_bucket;
+    for (int a = 0; a < 3; a++) {
+        const float l = (n_total - n_huge) ? ord2f(lo[a]) : 0.0f;
+        const float h = (n_total - n_huge) ? ord2f(hi[a]) : 0.0f;
+        info->lo[a] = l;
+        info->scale[a] = (h > l) ? 1024.0f / (h - l) : 0.0f;
+        info->scene_lo[a] = 0.0f;
+        info->scene_hi[a] = 0.0f;
+    }
+    for (uint32_t i = 0; i < kMaxHuge; i++) info->huge_slot[i] = (n_total - n_huge) + i;
+}
+
+// ------------------------------------------------------------------ K3: 30-bit Morton keys
+__device__ __forceinline__ uint32_t expand10(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__global__ void __launch_bounds__(256)
+k_morton(const float4 *__restrict__ w_geom, const float4 *__restrict__ tri_v12, uint32_t n,
+         const BuildInfo *__restrict__ info, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= n) return;
+    const Box3 b = prim_box(w_geom[gid], tri_v12);
+    uint32_t key;
+    if (extent_bucket(b) > info->huge_bucket) {
+        key = 0xFFFFFFFFu;
+    } else {
+        const float cx = 0.5f * (b.lo.x + b.hi.x), cy = 0.5f * (b.lo.y + b.hi.y), cz = 0.5f * (b.lo.z + b.hi.z);
+        const float qx = fminf(fmaxf((cx - info->lo[0]) * info->scale[0], 0.0f), 1023.0f);
+        const float qy = fminf(fmaxf((cy - info->lo[1]) * info->scale[1], 0.0f), 1023.0f);
+        const float qz = fminf(fmaxf((cz - info->lo[2]) * info->scale[2], 0.0f), 1023.0f);
+        key = (expand10((uint32_t)qx) << 2) | (expand10((uint32_t)qy) << 1) | expand10((uint32_t)qz);
+    }
+    keys[gid] = key;
+    vals[gid] = gid;
+}
+
+// ------------------------------------------------------------------ K4: LSD radix sort, 8-bit digits
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 keys per block
+
+__global__ void __launch_bounds__(kSortThreads)
+k_sort_hist(const uint32_t *__restrict__ keys, uint32_t n, int shift, uint32_t *__restrict__ ghist, uint32_t nblocks) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kSortTile;
+#pragma unroll
+    for (int j = 0; j < kSortItems; j++) {
+        const uint32_t i = base + j * kSortThreads + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    ghist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of `total` counters by one 1024-thread block (the table is small: 256 per tile)
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *__restrict__ g, uint32_t total) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    // coalesced tiles of 1024*4 counters, carried sequentially
+    for (uint32_t base = 0; base < total; base += 4096u) {
+        const uint32_t i0 = base + threadIdx.x * 4u;
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = (i0 + k < total) ? g[i0 + k] : 0u;
+        const uint32_t s = v[0] + v[1] + v[2] + v[3];
+        uint32_t inc = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (lane == 31) warp_sum[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t w = warp_sum[lane];
+            uint32_t winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, winc, o);
+                if (lane >= (uint32_t)o) winc += t;
+            }
+            warp_sum[lane] = winc - w;  // exclusive
+        }
+        __syncthreads();
+        uint32_t ex = carry + warp_sum[wid] + (inc - s);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (i0 + k < total) g[i0 + k] = ex;
+            ex += v[k];
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = ex;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+k_sort_scatter(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+               uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int shift,
+               const uint32_t *__restrict__ ghist, uint32_t nblocks) {
+    __shared__ uint32_t cnt[8][256];
+    for (int i = threadIdx.x; i < 8 * 256; i += kSortThreads) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t base = blockIdx.x * kSortTile + w * (kSortTile / 8);
+    uint32_t key[kSortItems];
+    uint16_t rank[kSortItems];
+#pragma unroll
+    for (int c = 0; c < kSortItems; c++) {
+        const uint32_t i = base + c * 32 + lane;
+        const bool valid = i < n;
+        key[c] = valid ? keys_in[i] : 0xFFFFFFFFu;
+        const uint32_t dg = valid ? ((key[c] >> shift) & 255u) : 256u;
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, dg);
+        const int leader = __ffs(peers) - 1;
+        uint32_t pre = 0;
+        if (valid && (int)lane == leader) {
+            pre = cnt[w][dg];
+            cnt[w][dg] = pre + __popc(peers);
+        }
+        pre = __shfl_sync(0xFFFFFFFFu, pre, leader);
+        rank[c] = (uint16_t)(pre + __popc(peers & lt));
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        const uint32_t dg = threadIdx.x;
+        uint32_t run = ghist[dg * nblocks + blockIdx.x];
+#pragma unroll
+        for (int ww = 0; ww < 8; ww++) {
+            const uint32_t t = cnt[ww][dg];
+            cnt[ww][dg] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < kSortItems; c++) {
+        const uint32_t i = base + c * 32 + lane;
+        if (i < n) {
+            const uint32_t dg = (key[c] >> shift) & 255u;
+            const uint32_t pos = cnt[w][dg] + rank[c];
+            keys_out[pos] = key[c];
+            vals_out[pos] = vals_in[i];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K5: gather primitives into Morton order
+__global__ void __launch_bounds__(256)
+k_gather(const uint32_t *__restrict__ vals, const float4 *__restrict__ w_geom, const uint32_t *__restrict__ w_mat,
+         uint32_t n, float4 *__restrict__ slot_geom, uint32_t *__restrict__ slot_prim, uint32_t *__restrict__ slot_mat) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t gid = vals[i];
+    slot_geom[i] = w_geom[gid];
+    slot_prim[i] = gid;
+    slot_mat[i] = w_mat[gid];
+}
+
+// ------------------------------------------------------------------ K6: Karras (2012) hierarchy
+// delta(i,j) = length of the common prefix of keys i and j; equal keys fall back to the index so
+// the tree is well defined for duplicate Morton codes.
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint32_t a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clz(a ^ b);
+}
+__device__ __forceinline__ int encode_child(int first, int last, int internal_idx, int leaf_max) {
+    const int cnt = last - first + 1;
+    if (cnt <= leaf_max) return (int)(kLeafFlag | ((uint32_t)(cnt - 1) << kLeafCountShift) | (uint32_t)first);
+    return internal_idx;
+}
+__global__ void __launch_bounds__(256)
+k_hierarchy(const uint32_t *__restrict__ keys, const BuildInfo *__restrict__ info, Node *__restrict__ nodes,
+            uint32_t *__restrict__ parent_int, uint32_t *__restrict__ parent_leaf, int leaf_max) {
+    const int n = (int)info->n_bvh;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < 2 || i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int split = i + s * d + min(d, 0);
+    const int first = min(i, j), last = max(i, j);
+    // topology links (always the full Karras tree: the refit climbs through collapsed nodes too)
+    if (split == first) parent_leaf[split] = ((uint32_t)i << 1) | 0u; else parent_int[split] = ((uint32_t)i << 1) | 0u;
+    if (split + 1 == last) parent_leaf[split + 1] = ((uint32_t)i << 1) | 1u; else parent_int[split + 1] = ((uint32_t)i << 1) | 1u;
+    if (i == 0) parent_int[0] = 0xFFFFFFFFu;
+    // child pointers seen by traversal: ranges of <= leaf_max prims become one leaf
+    const int c0 = encode_child(first, split, split, leaf_max);
+    const int c1 = encode_child(split + 1, last, split + 1, leaf_max);
+    nodes[i].n3 = make_float4(__int_as_float(c0), __int_as_float(c1), 0.0f, 0.0f);
+}
+
+// ------------------------------------------------------------------ K7: bottom-up refit
+__device__ __forceinline__ void store_child_box(Node *nd, uint32_t which, const Box3 &b) {
+    float4 *p = reinterpret_cast<float4 *>(nd);
+    if (which == 0) {
+        __stcg(p + 0, make_float4(b.lo.x, b.hi.x, b.lo.y, b.hi.y));
+        __stcg(reinterpret_cast<float2 *>(p + 2), make_float2(b.lo.z, b.hi.z));
+    } else {
+        __stcg(p + 1, make_float4(b.lo.x, b.hi.x, b.lo.y, b.hi.y));
+        __stcg(reinterpret_cast<float2 *>(p + 2) + 1, make_float2(b.lo.z, b.hi.z));
+    }
+}
+__global__ void __launch_bounds__(256)
+k_refit(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info,
+        Node *nodes, const uint32_t *__restrict__ parent_int, const uint32_t *__restrict__ parent_leaf,
+        uint32_t *visit) {
+    const uint32_t n = info->n_bvh;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < 2 || i >= n) return;
+    Box3 b = pad_box(prim_box(slot_geom[i], tri_v12));
+    uint32_t link = parent_leaf[i];
+    while (true) {
+        const uint32_t p = link >> 1, which = link & 1u;
+        store_child_box(nodes + p, which, b);
+        __threadfence();
+        if (atomicAdd(visit + p, 1u) == 0u) return;  // sibling not done yet
+        // second arriver: read the sibling's box (written before its fence) from L2
+        const float4 *q = reinterpret_cast<const float4 *>(nodes + p);
+        const float4 sxy = __ldcg(q + (which ^ 1u));
+        const float2 sz = __ldcg(reinterpret_cast<const float2 *>(q + 2) + (which ^ 1u));
+        b.lo = f3(fminf(b.lo.x, sxy.x), fminf(b.lo.y, sxy.z), fminf(b.lo.z, sz.x));
+        b.hi = f3(fmaxf(b.hi.x, sxy.y), fmaxf(b.hi.y, sxy.w), fmaxf(b.hi.z, sz.y));
+        link = parent_int[p];
+        if (link == 0xFFFFFFFFu) {
+            info->scene_lo[0] = b.lo.x; info->scene_lo[1] = b.lo.y; info->scene_lo[2] = b.lo.z;
+            info->scene_hi[0] = b.hi.x; info->scene_hi[1] = b.hi.y; info->scene_hi[2] = b.hi.z;
+            return;
+        }
+    }
+}
+
+// n_bvh <= 1: the root is the only node
+__global__ void k_small_tree(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info, Node *nodes) {
+    if (threadIdx.x || blockIdx.x) return;
+    const uint32_t n = info->n_bvh;
+    if (n >= 2) return;
+    const float inf = __int_as_float(0x7F800000);
+    Box3 e;
+    e.lo = f3(inf, inf, inf);
+    e.hi = f3(-inf, -inf, -inf);
+    Box3 b = e;
+    const int invalid = (int)(kLeafFlag | 0u);
+    int c0 = invalid;
+    if (n == 1) {
+        b = pad_box(prim_box(slot_geom[0], tri_v12));
+        c0 = (int)(kLeafFlag | 0u);
+        for (int a = 0; a < 3; a++) {
+            info->scene_lo[a] = a == 0 ? b.lo.x : (a == 1 ? b.lo.y : b.lo.z);
+            info->scene_hi[a] = a == 0 ? b.hi.x : (a == 1 ? b.hi.y : b.hi.z);
+        }
+    }
+    store_child_box(nodes, 0, b);
+    store_child_box(nodes, 1, e);
+    nodes[0].n3 = make_float4(__int_as_float(c0), __int_as_float(invalid), 0.0f, 0.0f);
+}
+
+// ------------------------------------------------------------------ host driver
+static inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+
+int build_accel(Scene *s, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    // ---- tables
+    uint64_t np = 0, nt = 0;
+    std::vector<uint32_t> base(s->insts.size() + 1);
+    for (size_t i = 0; i < s->insts.size(); i++) {
+        InstDev &in = s->insts[i];
+        const GroupDev &g = s->groups[in.group];
+        in.prim_base = (uint32_t)np;
+        in.tri_base = (uint32_t)nt;
+        base[i] = (uint32_t)np;
+        np += g.count;
+        if (g.kind == 1) nt += g.count;
+        if (g.kind == 0 && !in.identity) {
+            // spheres only support similarity transforms (uniform scale)
+            const float *m = in.m;
+            const float c0 = m[0] * m[0] + m[4] * m[4] + m[8] * m[8];
+            const float c1 = m[1] * m[1] + m[5] * m[5] + m[9] * m[9];
+            const float c2 = m[2] * m[2] + m[6] * m[6] + m[10] * m[10];
+            const float mx = fmaxf(c0, fmaxf(c1, c2)), mn = fminf(c0, fminf(c1, c2));
+            if (!(mx > 0.0f) || (mx - mn) > 1e-4f * mx)
+                return set_error(ctx, RT_ERR_UNSUPPORTED, "instance %zu: non-uniform scale on a sphere group", i);
+        }
+    }
+    base[s->insts.size()] = (uint32_t)np;
+    if (np >= (1ull << 27) && s->leaf_max > 1)
+        return set_error(ctx, RT_ERR_UNSUPPORTED, "more than 2^27 primitives (%llu)", (unsigned long long)np);
+    if (np >= 0x7FFFFFFFull) return set_error(ctx, RT_ERR_UNSUPPORTED, "too many primitives");
+    const uint32_t n = (uint32_t)np;
+    s->n_prims = n;
+    s->n_tris = (uint32_t)nt;
+
+    const size_t ng = s->groups.size() ? s->groups.size() : 1, ni = s->insts.size() ? s->insts.size() : 1;
+    RT_CUDA(ctx, s->d_groups.reserve(ng, &s->bytes));
+    RT_CUDA(ctx, s->d_insts.reserve(ni, &s->bytes));
+    RT_CUDA(ctx, s->d_inst_base.reserve(ni + 1, &s->bytes));
+    if (!s->groups.empty())
+        RT_CUDA(ctx, cudaMemcpyAsync(s->d_groups.p, s->groups.data(), s->groups.size() * sizeof(GroupDev), cudaMemcpyHostToDevice, st));
+    if (!s->insts.empty())
+        RT_CUDA(ctx, cudaMemcpyAsync(s->d_insts.p, s->insts.data(), s->insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, st));
+    RT_CUDA(ctx, cudaMemcpyAsync(s->d_inst_base.p, base.data(), base.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    // pageable sources: the copies above are staged before returning, so `base` may die here.
+
+    const size_t n1 = n ? n : 1;
+    const uint32_t sort_blocks = div_up(n ? n : 1, kSortTile);
+    RT_CUDA(ctx, s->w_geom.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->w_mat.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->tri_v12.reserve(2 * (nt ? nt : 1), &s->bytes));
+    RT_CUDA(ctx, s->tri_nrm.reserve(3 * (nt ? nt : 1), &s->bytes));
+    for (int k = 0; k < 2; k++) {
+        RT_CUDA(ctx, s->keys[k].reserve(n1, &s->bytes));
+        RT_CUDA(ctx, s->vals[k].reserve(n1, &s->bytes));
+    }
+    RT_CUDA(ctx, s->sort_hist.reserve(256 * (size_t)sort_blocks, &s->bytes));
+    RT_CUDA(ctx, s->bucket_tab.reserve(kExtentBuckets * 8, &s->bytes));
+    RT_CUDA(ctx, s->nodes.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->parent_int.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->parent_leaf.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->visit.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->slot_geom.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->slot_prim.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->slot_mat.reserve(n1, &s->bytes));
+    RT_CUDA(ctx, s->info.reserve(1, &s->bytes));
+
+    if (!s->ev[0]) {
+        for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&s->ev[k]));
+    }
+    RT_CUDA(ctx, cudaEventRecord(s->ev[0], st));
+
+    const uint32_t gb = div_up(n ? n : 1, 256);
+    k_init_buckets<<<div_up(kExtentBuckets * 8, 256), 256, 0, st>>>(s->bucket_tab.p);
+    RT_CUDA(ctx, cudaMemsetAsync(s->visit.p, 0, n1 * sizeof(uint32_t), st));
+    s->launches += 1;
+    if (n) {
+        k_flatten<<<gb, 256, 0, st>>>(s->d_insts.p, s->d_inst_base.p, (uint32_t)s->insts.size(), s->d_groups.p, n,
+                                      s->w_geom.p, s->w_mat.p, s->tri_v12.p, s->tri_nrm.p, s->bucket_tab.p);
+        s->launches += 1;
+    }
+    k_decide<<<1, 32, 0, st>>>(s->bucket_tab.p, n, s->info.p);
+    s->launches += 1;
+    if (n) {
+        k_morton<<<gb, 256, 0, st>>>(s->w_geom.p, s->tri_v12.p, n, s->info.p, s->keys[0].p, s->vals[0].p);
+        s->launches += 1;
+        int src = 0;
+        for (int pass = 0; pass < 4; pass++) {
+            const int shift = 8 * pass;
+            k_sort_hist<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[src].p, n, shift, s->sort_hist.p, sort_blocks);
+            k_sort_scan<<<1, 1024, 0, st>>>(s->sort_hist.p, 256u * sort_blocks);
+            k_sort_scatter<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[src].p, s->vals[src].p, s->keys[src ^ 1].p,
+                                                                 s->vals[src ^ 1].p, n, shift, s->sort_hist.p, sort_blocks);
+            src ^= 1;
+            s->launches += 3;
+        }
+        // 4 passes: result back in buffer 0
+        k_gather<<<gb, 256, 0, st>>>(s->vals[0].p, s->w_geom.p, s->w_mat.p, n, s->slot_geom.p, s->slot_prim.p, s->slot_mat.p);
+        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)s->leaf_max);
+        k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
+        s->launches += 3;
+    }
+    k_small_tree<<<1, 32, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p);
+    s->launches += 1;
+    RT_CUDA(ctx, cudaEventRecord(s->ev[1], st));
+    RT_CUDA(ctx, cudaGetLastError());
+    s->have_build_ev = true;
+    s->built = true;
+    s->last_stream = st;
+    return RT_OK;
+}
+
+SceneDev scene_dev(const Scene *s) {
+    SceneDev d;
+    d.nodes = s->nodes.p;
+    d.slot_geom = s->slot_geom.p;
+    d.slot_prim = s->slot_prim.p;
+    d.slot_mat = s->slot_mat.p;
+    d.tri_v12 = s->tri_v12.p;
+    d.tri_nrm = s->tri_nrm.p;
+    d.roughs = s->d_roughs.p;
+    d.metals = s->d_metals.p;
+    d.info = s->info.p;
+    return d;
+}
+
+}  // namespace rtb

@@ -1,0 +1,239 @@
+// rt_device.cuh — device maths, intersectors and BVH traversal.
+//
+// Floating-point contract: every translation unit that includes this header is
+// compiled with --fmad=false, so `a*b+c` is two IEEE roundings exactly as in the CPU oracle; IEEE
+// division and square root (nvcc defaults -prec-div=true -prec-sqrt=true).  Where a fused
+// multiply-add is wanted for speed and is parity-neutral (conservative box tests) it is requested
+// explicitly with __fmaf_rn.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_internal.h"
+
+namespace rtb {
+
+// include/Global/DeviceFunctions.cuh:18-19
+#define RT_ZERO 1e-6f
+#define RT_INF 1e16f
+
+struct F3 {
+    float x, y, z;
+};
+__device__ __forceinline__ F3 f3(float x, float y, float z) { return F3{x, y, z}; }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ F3 operator-(F3 a, F3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ F3 operator-(F3 a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ F3 operator*(F3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ F3 operator*(float s, F3 a) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ F3 operator/(F3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+// DeviceFunctions.cuh:407-409
+__device__ __forceinline__ float dot(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// DeviceFunctions.cuh:410-416
+__device__ __forceinline__ F3 cross(F3 a, F3 b) {
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+// DeviceFunctions.cuh:397-404 with IEEE 1/sqrt instead of the approximate rsqrtf
+__device__ __forceinline__ F3 normalize3(F3 a) {
+    const float l2 = dot(a, a);
+    if (l2 <= RT_ZERO * RT_ZERO) return f3(0.0f, 0.0f, 1.0f);
+    const float inv = 1.0f / sqrtf(l2);
+    return a * inv;
+}
+__device__ __forceinline__ bool finite3(F3 a) { return isfinite(a.x) && isfinite(a.y) && isfinite(a.z); }
+
+// ------------------------------------------------------------------ XORWOW in registers
+// Bit-identical to curand() / curand_uniform() of curand_kernel.h on a curandStateXORWOW whose
+// (d, v[0..4]) are these six words.
+struct Rng {
+    uint32_t d, v0, v1, v2, v3, v4;
+};
+__device__ __forceinline__ uint32_t rng_next(Rng &s) {
+    uint32_t t = s.v0 ^ (s.v0 >> 2);
+    s.v0 = s.v1;
+    s.v1 = s.v2;
+    s.v2 = s.v3;
+    s.v3 = s.v4;
+    s.v4 = (s.v4 ^ (s.v4 << 4)) ^ (t ^ (t << 1));
+    s.d += 362437u;
+    return s.v4 + s.d;
+}
+// curand_uniform: x * 2^-32 + 2^-33 (two roundings; curand_uniform.h _curand_uniform)
+__device__ __forceinline__ float rng_uniform(Rng &s) {
+    return (float)rng_next(s) * 2.3283064e-10f + (2.3283064e-10f / 2.0f);
+}
+// DeviceFunctions.cuh:220-222 + 570-582
+__device__ __forceinline__ F3 random_space_vector(Rng &s) {
+    F3 r;
+    float l2;
+    do {
+        r.x = -1.0f + (1.0f - (-1.0f)) * rng_uniform(s);
+        r.y = -1.0f + (1.0f - (-1.0f)) * rng_uniform(s);
+        r.z = -1.0f + (1.0f - (-1.0f)) * rng_uniform(s);
+        l2 = dot(r, r);
+    } while (l2 < RT_ZERO * RT_ZERO);
+    r = normalize3(r);
+    return r * 1.0f;
+}
+
+// ------------------------------------------------------------------ rays and hits
+struct Ray {
+    F3 o, d;
+    float tmin, tmax;
+};
+struct Hit {
+    float t;
+    uint32_t slot;  // kNoSlot = miss
+    float u, v;
+};
+
+// Robust ray/sphere (Haines et al., RT Gems ch.7); same operation order as oracle hit_sphere().
+__device__ __forceinline__ float hit_sphere(const Ray &r, float a, float inv_a, float4 s, bool self) {
+    const F3 f = r.o - f3(s.x, s.y, s.z);
+    const float bp = -dot(f, r.d);
+    const float k = bp * inv_a;
+    const F3 l = f + r.d * k;
+    const float disc = s.w * s.w - dot(l, l);
+    if (!(disc >= 0.0f)) return -1.0f;
+    const float cc = dot(f, f) - s.w * s.w;
+    const float sq = sqrtf(a * disc);
+    const float q = (bp >= 0.0f) ? (bp + sq) : (bp - sq);
+    const float t_cq = cc / q;
+    const float t_qa = q * inv_a;
+    const float t_near = (bp >= 0.0f) ? t_cq : t_qa;
+    const float t_far = (bp >= 0.0f) ? t_qa : t_cq;
+    if (self) {
+        const float t = (fabsf(t_near) <= fabsf(t_far)) ? t_far : t_near;
+        return (t > r.tmin && t < r.tmax) ? t : -1.0f;
+    }
+    if (t_near > r.tmin && t_near < r.tmax) return t_near;
+    if (t_far > r.tmin && t_far < r.tmax) return t_far;
+    return -1.0f;
+}
+
+// Moeller-Trumbore, two-sided; same operation order as oracle hit_triangle().
+__device__ __forceinline__ float hit_triangle(const Ray &r, F3 v0, F3 v1, F3 v2, float &u_out, float &v_out) {
+    const F3 e1 = v1 - v0;
+    const F3 e2 = v2 - v0;
+    const F3 p = cross(r.d, e2);
+    const float det = dot(e1, p);
+    if (!(det != 0.0f)) return -1.0f;
+    const float inv = 1.0f / det;
+    const F3 tv = r.o - v0;
+    const float u = dot(tv, p) * inv;
+    if (!(u >= 0.0f && u <= 1.0f)) return -1.0f;
+    const F3 q = cross(tv, e1);
+    const float v = dot(r.d, q) * inv;
+    if (!(v >= 0.0f && u + v <= 1.0f)) return -1.0f;
+    const float t = dot(e2, q) * inv;
+    if (!(t > r.tmin && t < r.tmax)) return -1.0f;
+    u_out = u;
+    v_out = v;
+    return t;
+}
+
+__device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+
+// Test the primitive stored in `slot` and keep the closest hit; ties -> smaller global prim id.
+__device__ __forceinline__ void test_slot(const SceneDev &sc, const Ray &r, float a, float inv_a,
+                                          uint32_t slot, uint32_t skip_slot, Hit &best) {
+    const float4 g = ldg4(sc.slot_geom + slot);
+    float t, u = 0.0f, v = 0.0f;
+    const uint32_t wb = __float_as_uint(g.w);
+    if (!(wb & 0x80000000u)) {
+        t = hit_sphere(r, a, inv_a, g, slot == skip_slot);
+    } else {
+        if (slot == skip_slot) return;
+        const uint32_t ti = wb & 0x7FFFFFFFu;
+        const float4 a1 = ldg4(sc.tri_v12 + 2 * (size_t)ti);
+        const float4 a2 = ldg4(sc.tri_v12 + 2 * (size_t)ti + 1);
+        t = hit_triangle(r, f3(g.x, g.y, g.z), f3(a1.x, a1.y, a1.z), f3(a2.x, a2.y, a2.z), u, v);
+    }
+    if (t < 0.0f) return;
+    bool take = t < best.t;
+    if (t == best.t && best.slot != kNoSlot) take = __ldg(sc.slot_prim + slot) < __ldg(sc.slot_prim + best.slot);
+    if (take) {
+        best.t = t;
+        best.slot = slot;
+        best.u = u;
+        best.v = v;
+    }
+}
+
+#define RT_STACK 64
+
+// Closest hit through the LBVH.  Boxes were padded at build time and the far bound is widened by
+// 2e-6 relative, so no valid hit can be culled: the result equals brute force over all prims.
+__device__ __forceinline__ Hit trace(const SceneDev &sc, const Ray &r, uint32_t skip_slot) {
+    Hit best;
+    best.t = r.tmax;
+    best.slot = kNoSlot;
+    best.u = best.v = 0.0f;
+    const float a = dot(r.d, r.d);
+    const float inv_a = 1.0f / a;
+
+    const BuildInfo *info = sc.info;
+    const uint32_t n_huge = info->n_huge;
+    for (uint32_t i = 0; i < n_huge; i++) test_slot(sc, r, a, inv_a, info->huge_slot[i], skip_slot, best);
+    if (info->n_bvh == 0) {
+        if (best.slot == kNoSlot) best.t = RT_INF;
+        return best;
+    }
+
+    // reciprocal direction, clamped so that 0 * inf never appears
+    const float ex = fabsf(r.d.x) < 1e-30f ? copysignf(1e-30f, r.d.x) : r.d.x;
+    const float ey = fabsf(r.d.y) < 1e-30f ? copysignf(1e-30f, r.d.y) : r.d.y;
+    const float ez = fabsf(r.d.z) < 1e-30f ? copysignf(1e-30f, r.d.z) : r.d.z;
+    const float ix = 1.0f / ex, iy = 1.0f / ey, iz = 1.0f / ez;
+    const float ox = -r.o.x * ix, oy = -r.o.y * iy, oz = -r.o.z * iz;
+
+    int stack[RT_STACK];
+    int sp = 0;
+    int node = 0;
+    const float4 *nodes = reinterpret_cast<const float4 *>(sc.nodes);
+
+    while (true) {
+        if (node >= 0) {
+            const float4 n0 = ldg4(nodes + 4 * (size_t)node);
+            const float4 n1 = ldg4(nodes + 4 * (size_t)node + 1);
+            const float4 n2 = ldg4(nodes + 4 * (size_t)node + 2);
+            const float4 n3 = ldg4(nodes + 4 * (size_t)node + 3);
+            const float c0x0 = __fmaf_rn(n0.x, ix, ox), c0x1 = __fmaf_rn(n0.y, ix, ox);
+            const float c0y0 = __fmaf_rn(n0.z, iy, oy), c0y1 = __fmaf_rn(n0.w, iy, oy);
+            const float c0z0 = __fmaf_rn(n2.x, iz, oz), c0z1 = __fmaf_rn(n2.y, iz, oz);
+            const float c1x0 = __fmaf_rn(n1.x, ix, ox), c1x1 = __fmaf_rn(n1.y, ix, ox);
+            const float c1y0 = __fmaf_rn(n1.z, iy, oy), c1y1 = __fmaf_rn(n1.w, iy, oy);
+            const float c1z0 = __fmaf_rn(n2.z, iz, oz), c1z1 = __fmaf_rn(n2.w, iz, oz);
+            const float lo0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), r.tmin));
+            const float hi0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
+            const float lo1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), r.tmin));
+            const float hi1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
+            const bool h0 = lo0 <= hi0 * 1.000002f;
+            const bool h1 = lo1 <= hi1 * 1.000002f;
+            const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
+            if (h0 && h1) {
+                const bool swap = lo1 < lo0;
+                node = swap ? ch1 : ch0;
+                if (sp < RT_STACK) stack[sp++] = swap ? ch0 : ch1;
+            } else if (h0) {
+                node = ch0;
+            } else if (h1) {
+                node = ch1;
+            } else {
+                if (sp == 0) break;
+                node = stack[--sp];
+            }
+        } else {
+            const uint32_t enc = (uint32_t)node;
+            const uint32_t first = enc & kLeafFirstMask;
+            const uint32_t cnt = ((enc >> kLeafCountShift) & 7u) + 1u;
+            for (uint32_t i = 0; i < cnt; i++) test_slot(sc, r, a, inv_a, first + i, skip_slot, best);
+            if (sp == 0) break;
+            node = stack[--sp];
+        }
+    }
+    if (best.slot == kNoSlot) best.t = RT_INF;
+    return best;
+}
+
+}  // namespace rtb

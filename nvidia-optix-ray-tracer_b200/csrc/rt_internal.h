@@ -1,0 +1,196 @@
+// rt_internal.h — host-side structures shared by the C-ABI implementation files.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rtb200.h"
+
+namespace rtb {
+
+// ------------------------------------------------------------------ device-visible records
+struct GroupDev {
+    const float *a;  // spheres: float3 centers[n]    triangles: float3 vertices[3n]
+    const float *b;  // spheres: float radii[n]       triangles: float3 normals[3n]
+    uint32_t count;
+    uint32_t kind;  // 0 sphere, 1 triangle
+};
+
+struct InstDev {
+    float m[12];         // row-major 3x4 (OptixInstance.transform)
+    uint32_t group;
+    uint32_t mat;        // (mat_type << 31) | mat_index
+    uint32_t mat_stride;
+    uint32_t prim_base;  // global id of this instance's first primitive
+    uint32_t tri_base;   // index of its first triangle in the world triangle arrays
+    uint32_t identity;   // linear part is exactly I (spheres keep r, normals untouched)
+    uint32_t pad0, pad1;
+};
+static_assert(sizeof(InstDev) == 80, "InstDev layout");
+
+// 64-byte BVH2 node: both children's boxes live in the parent (one 4x128-bit fetch per visit).
+//   n0 = c0.lo.x c0.hi.x c0.lo.y c0.hi.y
+//   n1 = c1.lo.x c1.hi.x c1.lo.y c1.hi.y
+//   n2 = c0.lo.z c0.hi.z c1.lo.z c1.hi.z
+//   n3 = child0 child1 (as int bits) ; unused ; unused
+// child >= 0: internal node index.  child < 0: leaf, bits 0..26 first slot, bits 27..29 count-1.
+struct alignas(16) Node {
+    float4 n0, n1, n2, n3;
+};
+
+constexpr uint32_t kLeafFlag = 0x80000000u;
+constexpr uint32_t kLeafFirstMask = 0x07FFFFFFu;
+constexpr int kLeafCountShift = 27;
+constexpr uint32_t kMaxHuge = 16;
+constexpr uint32_t kExtentBuckets = 96;  // floor(log2(extent)) + 64 clamped to [0,95]
+constexpr uint32_t kNoSlot = 0xFFFFFFFFu;
+
+// Written by the build kernels, read by later build kernels and by traversal (device memory).
+struct BuildInfo {
+    float lo[3];          // centroid bounds of the non-huge prims (Morton frame)
+    float scale[3];       // 1024 / extent per axis
+    uint32_t n_total;
+    uint32_t n_bvh;       // prims inside the BVH ( = n_total - n_huge )
+    uint32_t n_huge;
+    int32_t huge_bucket;  // prims whose extent bucket is > this are "huge"
+    float scene_lo[3], scene_hi[3];  // root bounds after refit
+    uint32_t huge_slot[kMaxHuge];    // slots (sorted order positions) of huge prims
+};
+
+struct SceneDev {  // everything a traversal needs, passed by value to kernels
+    const Node *nodes;
+    const float4 *slot_geom;    // sphere: c.xyz r   | triangle: v0.xyz, bits(0x80000000|tri index)
+    const uint32_t *slot_prim;  // global primitive id per slot
+    const uint32_t *slot_mat;   // (mat_type<<31)|index per slot
+    const float4 *tri_v12;      // 2 per triangle: v1.xyz _, v2.xyz _
+    const float4 *tri_nrm;      // 3 per triangle: world-space vertex normals
+    const float4 *roughs;       // rgb _
+    const float4 *metals;       // rgb fuzz
+    const BuildInfo *info;
+};
+
+// ------------------------------------------------------------------ host-side helpers
+template <typename T>
+struct DevBuf {  // grow-only device buffer
+    T *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n, size_t *total_bytes) {
+        if (n <= cap) return cudaSuccess;
+        if (p) {
+            cudaError_t e = cudaFree(p);
+            if (e != cudaSuccess) return e;
+            *total_bytes -= cap * sizeof(T);
+            p = nullptr;
+            cap = 0;
+        }
+        size_t want = n + n / 16 + 64;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e != cudaSuccess) return e;
+        cap = want;
+        *total_bytes += cap * sizeof(T);
+        return cudaSuccess;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct Context {
+    int device = 0;
+    int sm_count = 148;
+    std::mutex mu;
+    std::string last_error;
+};
+
+struct GroupHost {
+    GroupDev d;
+};
+struct InstHost {
+    InstDev d;
+};
+
+struct Scene {
+    Context *ctx = nullptr;
+    std::vector<GroupDev> groups;
+    std::vector<InstDev> insts;
+    bool topo_dirty = true;   // groups/instances changed -> re-upload tables
+    bool built = false;
+    uint32_t n_prims = 0, n_tris = 0;
+    uint32_t leaf_max = 4;
+    uint32_t batch_spp = 4;
+    size_t bytes = 0;
+    uint64_t launches = 0;
+
+    // tables
+    DevBuf<GroupDev> d_groups;
+    DevBuf<InstDev> d_insts;
+    DevBuf<uint32_t> d_inst_base;
+    DevBuf<float4> d_roughs, d_metals;
+    size_t n_rough = 0, n_metal = 0;
+
+    // build
+    DevBuf<float4> w_geom;     // per global prim
+    DevBuf<uint32_t> w_mat;    // per global prim
+    DevBuf<float4> tri_v12;    // 2 per tri
+    DevBuf<float4> tri_nrm;    // 3 per tri
+    DevBuf<uint32_t> keys[2], vals[2];
+    DevBuf<uint32_t> sort_hist;  // 256 * blocks
+    DevBuf<uint32_t> bucket_tab; // kExtentBuckets * 8
+    DevBuf<Node> nodes;
+    DevBuf<uint32_t> parent_int, parent_leaf, visit;
+    DevBuf<float4> slot_geom;
+    DevBuf<uint32_t> slot_prim, slot_mat;
+    DevBuf<BuildInfo> info;
+
+    // render
+    DevBuf<float4> phit;          // per pixel: t, bits(slot), u, v
+    DevBuf<uint32_t> rng_base;    // 6 words per pixel (pristine) SoA: [6][npix]
+    DevBuf<uint32_t> rng_cur;     // working copy
+    uint64_t rng_seed = 0;
+    uint32_t rng_w = 0, rng_h = 0, rng_off = 0;  // key of rng_base
+    uint64_t rng_cur_off = ~0ull;                // sample offset rng_cur currently sits at
+    bool rng_valid = false;
+    DevBuf<float4> q_o[2], q_d[2], q_t[2];
+    DevBuf<uint4> q_r[2];
+    DevBuf<uint32_t> q_r4[2];
+    DevBuf<float4> result;        // per path
+    DevBuf<uint32_t> counters;    // queue counters
+    DevBuf<unsigned long long> seg_total;
+
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool have_build_ev = false, have_render_ev = false;
+    cudaStream_t last_stream = nullptr;
+    uint64_t last_primary = 0;
+    size_t last_n_cnt = 0;
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_ev;  // pairs around traversal launches
+    size_t prof_used = 0;
+};
+
+int set_error(Context *ctx, int code, const char *fmt, ...);
+
+#define RT_CUDA(ctx, expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess)                                                               \
+            return rtb::set_error((ctx), _e == cudaErrorMemoryAllocation ? RT_ERR_OOM : RT_ERR_CUDA, \
+                                  "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+// implemented in rt_build.cu / rt_render.cu
+int build_accel(Scene *s, cudaStream_t stream);
+int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *p, const rt_outputs *out,
+                 cudaStream_t stream);
+int resolve(Context *ctx, const float *accum, size_t n, float *color, uint8_t *rgba8, cudaStream_t stream);
+int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id,
+               cudaStream_t stream);
+SceneDev scene_dev(const Scene *s);
+
+}  // namespace rtb

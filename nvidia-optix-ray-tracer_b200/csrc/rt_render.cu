@@ -1,0 +1,481 @@
+// rt_render.cu — wavefront path tracer kernels for sm_100a.
+//
+// Replaces the OptiX programs of the reference:
+//   __raygen__raygenProgram            shader/Shader.cu:246-273   -> k_primary / k_shade_primary
+//   closesthitImpl (4 closest-hit PGs) shader/Shader.cu:94-242    -> scatter()
+//   __miss__missProgram                shader/Shader.cu:276-287   -> miss branches
+//   __initializeDeviceRandomGenerators src/Global/HostFunctions.cu:122-136 -> k_rng_init
+//   colorToFloat4 / convertFloat4ToUchar4Kernel  DeviceFunctions.cuh:153-212,
+//                                      src/Global/RendererImpl.cu:672-678 -> k_resolve
+// The reference's recursion (optixTrace inside closest-hit, depth <= rayTraceDepth) becomes an
+// iterative wavefront: one kernel per bounce over a compacted SoA ray queue.
+#include <curand_kernel.h>
+
+#include <algorithm>
+
+#include "rt_device.cuh"
+
+namespace rtb {
+
+struct CamDev {
+    F3 c, U, V, W;
+};
+
+struct Queue {
+    float4 *o;    // origin.xyz, bits(path id)
+    float4 *d;    // dir.xyz, bits(skip slot)
+    float4 *t;    // throughput.rgb, bits(rng.d)
+    uint4 *r;     // rng v0..v3
+    uint32_t *r4; // rng v4
+};
+
+// ------------------------------------------------------------------ pixel <-> thread mapping (8x4 tiles)
+__device__ __forceinline__ bool tile_pixel(uint32_t tid, uint32_t W, uint32_t H, uint32_t &x, uint32_t &y) {
+    const uint32_t tiles_x = (W + 7u) >> 3;
+    const uint32_t tile = tid >> 5, lane = tid & 31u;
+    x = (tile % tiles_x) * 8u + (lane & 7u);
+    y = (tile / tiles_x) * 4u + (lane >> 3);
+    return x < W && y < H;
+}
+
+// shader/Shader.cu:249-261
+__device__ __forceinline__ Ray primary_ray(const CamDev &cam, uint32_t x, uint32_t y, uint32_t W, uint32_t H) {
+    const float nx = (((float)x + 0.5f) / (float)W) * 2.0f - 1.0f;
+    const float ny = (((float)y + 0.5f) / (float)H) * 2.0f - 1.0f;
+    const float aspect = (float)W / (float)H;
+    Ray r;
+    r.o = cam.c;
+    r.d = normalize3(nx * aspect * cam.U + ny * cam.V + cam.W);
+    r.tmin = RT_ZERO;
+    r.tmax = RT_INF;
+    return r;
+}
+
+// ------------------------------------------------------------------ RNG state init (HostFunctions.cu:122-127)
+// seed fixed by the caller (the reference xors clock64() in: quirk 7), subsequence = pixel,
+// offset = sample_offset * 64; bounds-checked and unpadded (quirk 8).
+__global__ void __launch_bounds__(128)
+k_rng_init(uint32_t *__restrict__ rng, uint32_t npix, unsigned long long seed, unsigned long long offset) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    curandStateXORWOW st;
+    curand_init(seed, (unsigned long long)p, offset, &st);
+    rng[0 * (size_t)npix + p] = st.d;
+    rng[1 * (size_t)npix + p] = st.v[0];
+    rng[2 * (size_t)npix + p] = st.v[1];
+    rng[3 * (size_t)npix + p] = st.v[2];
+    rng[4 * (size_t)npix + p] = st.v[3];
+    rng[5 * (size_t)npix + p] = st.v[4];
+}
+
+// ------------------------------------------------------------------ closest-hit shading (Shader.cu:94-242)
+struct Scatter {
+    F3 P, dir, alb, N;
+};
+__device__ __forceinline__ Scatter scatter(const SceneDev &sc, const Ray &ray, const Hit &hit, Rng &rng) {
+    Scatter s;
+    s.P = ray.o + hit.t * ray.d;  // :114
+    const float4 g = ldg4(sc.slot_geom + hit.slot);
+    const uint32_t wb = __float_as_uint(g.w);
+    F3 N;
+    if (!(wb & 0x80000000u)) {  // :122-136, world-space centre
+        const F3 on = (s.P - f3(g.x, g.y, g.z)) / g.w;
+        N = (dot(ray.d, on) < 0.0f) ? on : -on;
+    } else {  // :137-155
+        const uint32_t ti = wb & 0x7FFFFFFFu;
+        const float4 n1 = ldg4(sc.tri_nrm + 3 * (size_t)ti);
+        const float4 n2 = ldg4(sc.tri_nrm + 3 * (size_t)ti + 1);
+        const float4 n3 = ldg4(sc.tri_nrm + 3 * (size_t)ti + 2);
+        const float u = hit.u, v = hit.v;
+        const float w = 1.0f - u - v;
+        const F3 nn = w * f3(n1.x, n1.y, n1.z) + u * f3(n2.x, n2.y, n2.z) + v * f3(n3.x, n3.y, n3.z);
+        N = (dot(ray.d, nn) < 0.0f) ? nn : -nn;
+    }
+    const uint32_t m = __ldg(sc.slot_mat + hit.slot);
+    const uint32_t mi = m & 0x7FFFFFFFu;
+    F3 dir;
+    if (!(m >> 31)) {  // ROUGH :169-179
+        const float4 a = ldg4(sc.roughs + mi);
+        dir = N + random_space_vector(rng);
+        if (fabsf(dot(dir, dir) - RT_ZERO * RT_ZERO) < RT_ZERO) dir = N;
+        s.alb = f3(a.x, a.y, a.z);
+    } else {  // METAL :180-192
+        const float4 a = ldg4(sc.metals + mi);
+        const F3 vv = ray.d;
+        dir = normalize3(vv - 2 * dot(vv, N) * N);
+        if (a.w > 0.0f) dir = dir + a.w * random_space_vector(rng);
+        s.alb = f3(a.x, a.y, a.z);
+    }
+    // :202-213
+    if (!finite3(dir) || dot(dir, dir) <= RT_ZERO * RT_ZERO) {
+        dir = N;
+        if (dot(dir, dir) <= RT_ZERO * RT_ZERO || !finite3(dir)) dir = f3(0.0f, 0.0f, 1.0f);
+    }
+    s.dir = dir;
+    s.N = N;
+    return s;
+}
+
+// warp-aggregated queue append; returns the slot for lanes with emit == true
+__device__ __forceinline__ uint32_t queue_push(uint32_t *counter, bool emit) {
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, emit);
+    if (!mask) return 0;
+    const uint32_t lane = threadIdx.x & 31u;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ void queue_write(const Queue &q, uint32_t i, F3 o, F3 d, F3 thr, uint32_t pid,
+                                            uint32_t skip, const Rng &r) {
+    q.o[i] = make_float4(o.x, o.y, o.z, __uint_as_float(pid));
+    q.d[i] = make_float4(d.x, d.y, d.z, __uint_as_float(skip));
+    q.t[i] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(r.d));
+    q.r[i] = make_uint4(r.v0, r.v1, r.v2, r.v3);
+    q.r4[i] = r.v4;
+}
+
+// ------------------------------------------------------------------ primary visibility (one ray per pixel)
+__global__ void __launch_bounds__(128)
+k_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, float4 *__restrict__ phit, uint32_t *__restrict__ prim_id,
+          float4 *__restrict__ albedo, float4 *__restrict__ normal) {
+    uint32_t x, y;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y)) return;
+    const size_t p = (size_t)y * W + x;  // Shader.cu:270
+    const Ray r = primary_ray(cam, x, y, W, H);
+    const Hit h = trace(sc, r, kNoSlot);
+    phit[p] = make_float4(h.t, __uint_as_float(h.slot), h.u, h.v);
+    if (prim_id) prim_id[p] = (h.slot == kNoSlot) ? RT_MISS_ID : __ldg(sc.slot_prim + h.slot);
+    if (albedo || normal) {
+        float4 a = make_float4(0, 0, 0, 0), n = make_float4(0, 0, 0, 0);  // Shader.cu:284-286
+        if (h.slot != kNoSlot) {
+            // first-hit AOVs, Shader.cu:216-227 (never consumes RNG: fuzz/rough draws excluded)
+            Rng dummy = {0, 1, 2, 3, 4, 5};
+            const Scatter s = scatter(sc, r, h, dummy);
+            const F3 nn = normalize3(s.N);
+            a = make_float4(s.alb.x, s.alb.y, s.alb.z, 1.0f);
+            n = make_float4(nn.x, nn.y, nn.z, 0.0f);
+        }
+        if (albedo) albedo[p] = a;
+        if (normal) normal[p] = n;
+    }
+}
+
+// ------------------------------------------------------------------ first bounce for S samples of every pixel
+// The reference has no sub-pixel jitter (Shader.cu:249-252), so all samples of a pixel share the
+// primary hit; each sample continues with its own XORWOW stream(p, s).
+__global__ void __launch_bounds__(128)
+k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
+                const float4 *__restrict__ phit, uint32_t *__restrict__ rng, Queue out, uint32_t *out_count,
+                float4 *__restrict__ result) {
+    uint32_t x, y;
+    const bool valid = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y);
+    const uint32_t npix = W * H;
+    const uint32_t p = valid ? y * W + x : 0u;
+    Ray ray;
+    Hit hit;
+    Rng st = {0, 0, 0, 0, 0, 0};
+    hit.slot = kNoSlot;
+    if (valid) {
+        ray = primary_ray(cam, x, y, W, H);
+        const float4 h = phit[p];
+        hit.t = h.x;
+        hit.slot = __float_as_uint(h.y);
+        hit.u = h.z;
+        hit.v = h.w;
+        st.d = rng[0 * (size_t)npix + p];
+        st.v0 = rng[1 * (size_t)npix + p];
+        st.v1 = rng[2 * (size_t)npix + p];
+        st.v2 = rng[3 * (size_t)npix + p];
+        st.v3 = rng[4 * (size_t)npix + p];
+        st.v4 = rng[5 * (size_t)npix + p];
+    }
+    const bool is_hit = valid && hit.slot != kNoSlot;
+    const bool go = is_hit && max_depth > 1u;  // Shader.cu:102-107 with depth == 1
+    for (uint32_t s = 0; s < S; s++) {
+        const size_t pid = (size_t)p * S + s;
+        Scatter sc1;
+        Rng r = st;
+        if (go) sc1 = scatter(sc, ray, hit, r);
+        const uint32_t qi = queue_push(out_count, go);
+        if (go) {
+            queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, hit.slot, r);
+        } else if (valid) {
+            // miss: 1 * background (Shader.cu:276-287); depth cut-off: 0 (:102-107)
+            result[pid] = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
+        }
+        if (valid) {
+#pragma unroll 8
+            for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
+        }
+    }
+    if (valid) {
+        rng[0 * (size_t)npix + p] = st.d;
+        rng[1 * (size_t)npix + p] = st.v0;
+        rng[2 * (size_t)npix + p] = st.v1;
+        rng[3 * (size_t)npix + p] = st.v2;
+        rng[4 * (size_t)npix + p] = st.v3;
+        rng[5 * (size_t)npix + p] = st.v4;
+    }
+}
+
+// ------------------------------------------------------------------ one bounce over the ray queue (persistent)
+__global__ void __launch_bounds__(128)
+k_bounce(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, Queue out, uint32_t *out_count,
+         float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg) {
+    const uint32_t n = *in_count;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; w0 < n; w0 += stride) {
+        const uint32_t i = w0 + (threadIdx.x & 31u);
+        const bool valid = i < n;
+        bool emit = false;
+        Scatter s;
+        Rng r;
+        F3 thr;
+        uint32_t pid = 0, slot = kNoSlot;
+        if (valid) {
+            const float4 o = in.o[i], d = in.d[i], t = in.t[i];
+            Ray ray;
+            ray.o = f3(o.x, o.y, o.z);
+            ray.d = f3(d.x, d.y, d.z);
+            ray.tmin = RT_ZERO;  // Shader.cu:231-233
+            ray.tmax = RT_INF;
+            pid = __float_as_uint(o.w);
+            thr = f3(t.x, t.y, t.z);
+            const Hit h = trace(sc, ray, __float_as_uint(d.w));
+            if (h.slot == kNoSlot) {
+                result[pid] = make_float4(thr.x * bg.x, thr.y * bg.y, thr.z * bg.z, 0.0f);
+            } else if (depth >= max_depth) {
+                result[pid] = make_float4(0, 0, 0, 0);
+            } else {
+                const uint4 rv = in.r[i];
+                r.d = __float_as_uint(t.w);
+                r.v0 = rv.x; r.v1 = rv.y; r.v2 = rv.z; r.v3 = rv.w;
+                r.v4 = in.r4[i];
+                s = scatter(sc, ray, h, r);
+                thr = f3(thr.x * s.alb.x, thr.y * s.alb.y, thr.z * s.alb.z);  // Shader.cu:236-238
+                slot = h.slot;
+                emit = true;
+            }
+        }
+        const uint32_t qi = queue_push(out_count, emit);
+        if (emit) queue_write(out, qi, s.P, s.dir, thr, pid, slot, r);
+    }
+}
+
+// ------------------------------------------------------------------ ordered accumulation of a sample batch
+__global__ void __launch_bounds__(256)
+k_accumulate(const float4 *__restrict__ result, uint32_t S, uint32_t npix, float4 *__restrict__ accum, int fresh) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    float4 a = fresh ? make_float4(0, 0, 0, 0) : accum[p];
+    for (uint32_t s = 0; s < S; s++) {
+        const float4 r = result[(size_t)p * S + s];
+        a.x += r.x;
+        a.y += r.y;
+        a.z += r.z;
+    }
+    a.w += (float)S;
+    accum[p] = a;
+}
+
+// ------------------------------------------------------------------ resolve: mean, clamp, sRGB, quantise
+// DeviceFunctions.cuh:153-212
+__device__ __forceinline__ float srgb(float c) {
+    const float cx = fmaxf(0.0f, fminf(c, 1.0f));
+    const float px = powf(cx, 1.0f / 2.4f);
+    const float sx = cx < 0.0031308f ? 12.92f * cx : 1.055f * px - 0.055f;
+    return fmaxf(0.0f, fminf(sx, 1.0f));
+}
+__global__ void __launch_bounds__(256)
+k_resolve(const float4 *__restrict__ accum, size_t n, float4 *__restrict__ color, uchar4 *__restrict__ rgba8) {
+    const size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const float4 a = accum[p];
+    const float inv = a.w > 0.0f ? 1.0f / a.w : 0.0f;
+    const float sx = srgb(a.x * inv), sy = srgb(a.y * inv), sz = srgb(a.z * inv);
+    if (color) color[p] = make_float4(sx, sy, sz, 1.0f);
+    if (rgba8)
+        rgba8[p] = make_uchar4((unsigned char)min((unsigned int)(sx * 256.0f), 255u),
+                               (unsigned char)min((unsigned int)(sy * 256.0f), 255u),
+                               (unsigned char)min((unsigned int)(sz * 256.0f), 255u), 255);
+}
+
+// ------------------------------------------------------------------ validation: caller-supplied rays
+__global__ void __launch_bounds__(128)
+k_trace_rays(SceneDev sc, const float *__restrict__ rays, const uint32_t *__restrict__ skip_gid,
+             const uint32_t *__restrict__ gid_to_slot, uint32_t n, float *__restrict__ out_t, uint32_t *__restrict__ out_id) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Ray r;
+    r.o = f3(rays[8 * (size_t)i], rays[8 * (size_t)i + 1], rays[8 * (size_t)i + 2]);
+    r.tmin = rays[8 * (size_t)i + 3];
+    r.d = f3(rays[8 * (size_t)i + 4], rays[8 * (size_t)i + 5], rays[8 * (size_t)i + 6]);
+    r.tmax = rays[8 * (size_t)i + 7];
+    uint32_t skip = kNoSlot;
+    if (skip_gid && skip_gid[i] != RT_MISS_ID) skip = gid_to_slot[skip_gid[i]];
+    const Hit h = trace(sc, r, skip);
+    out_t[i] = (h.slot == kNoSlot) ? __int_as_float(0x7F800000) : h.t;
+    out_id[i] = (h.slot == kNoSlot) ? RT_MISS_ID : sc.slot_prim[h.slot];
+}
+__global__ void k_invert_slots(const uint32_t *__restrict__ slot_prim, uint32_t n, uint32_t *__restrict__ gid_to_slot) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) gid_to_slot[slot_prim[i]] = i;
+}
+
+// cumulative segment counter (device side, so that no host read is needed between frames)
+__global__ void k_tally(const uint32_t *__restrict__ counters, uint32_t n_cnt, uint32_t primary, unsigned long long *total) {
+    if (threadIdx.x || blockIdx.x) return;
+    unsigned long long s = primary;
+    for (uint32_t i = 0; i < n_cnt; i++) s += counters[i];
+    *total += s;
+}
+
+// ------------------------------------------------------------------ host drivers
+static inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+
+// optional per-launch timing of the traversal kernels (rt_scene_set_option "profile")
+static cudaError_t prof_mark(Scene *s, cudaStream_t st) {
+    if (!s->profile) return cudaSuccess;
+    if (s->prof_used == s->prof_ev.size()) {
+        cudaEvent_t e;
+        cudaError_t err = cudaEventCreate(&e);
+        if (err != cudaSuccess) return err;
+        s->prof_ev.push_back(e);
+    }
+    return cudaEventRecord(s->prof_ev[s->prof_used++], st);
+}
+
+static Queue make_queue(Scene *s, int k) { return Queue{s->q_o[k].p, s->q_d[k].p, s->q_t[k].p, s->q_r[k].p, s->q_r4[k].p}; }
+
+int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, const rt_outputs *out, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_render before rt_accel_build");
+    const uint32_t W = fp->width, H = fp->height;
+    if (!W || !H || (uint64_t)W * H >= (1ull << 31)) return set_error(ctx, RT_ERR_INVALID, "bad image size %ux%u", W, H);
+    if (fp->max_depth > 255) return set_error(ctx, RT_ERR_INVALID, "max_depth %u too large", fp->max_depth);
+    if (fp->max_depth > 1 && 3ull * (fp->max_depth - 1) > RT_RNG_SAMPLE_STRIDE)
+        return set_error(ctx, RT_ERR_INVALID, "max_depth %u exceeds the RNG stride budget", fp->max_depth);
+    const uint32_t npix = W * H;
+    const uint32_t spp = out->accum_linear ? fp->spp : 0u;
+    const uint32_t Sb = s->batch_spp ? s->batch_spp : 1u;
+    if ((uint64_t)npix * Sb >= (1ull << 32)) return set_error(ctx, RT_ERR_INVALID, "batch too large");
+    const uint32_t n_batches = spp ? div_up(spp, Sb) : 0u;
+    const uint32_t D = fp->max_depth;
+
+    RT_CUDA(ctx, s->phit.reserve(npix, &s->bytes));
+    if (spp) {
+        RT_CUDA(ctx, s->rng_base.reserve(6 * (size_t)npix, &s->bytes));
+        RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
+        const size_t qn = (size_t)npix * std::min(Sb, spp);
+        for (int k = 0; k < 2; k++) {
+            RT_CUDA(ctx, s->q_o[k].reserve(qn, &s->bytes));
+            RT_CUDA(ctx, s->q_d[k].reserve(qn, &s->bytes));
+            RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
+            RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
+            RT_CUDA(ctx, s->q_r4[k].reserve(qn, &s->bytes));
+        }
+        RT_CUDA(ctx, s->result.reserve(qn, &s->bytes));
+    }
+    const size_t n_cnt = (size_t)(n_batches ? n_batches : 1) * (D + 3);
+    RT_CUDA(ctx, s->counters.reserve(n_cnt, &s->bytes));
+    if (!s->seg_total.p) {
+        RT_CUDA(ctx, s->seg_total.reserve(1, &s->bytes));
+        RT_CUDA(ctx, cudaMemsetAsync(s->seg_total.p, 0, sizeof(unsigned long long), st));
+    }
+    if (!s->ev[0])
+        for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&s->ev[k]));
+
+    RT_CUDA(ctx, cudaEventRecord(s->ev[2], st));
+    RT_CUDA(ctx, cudaMemsetAsync(s->counters.p, 0, n_cnt * sizeof(uint32_t), st));
+
+    const SceneDev sd = scene_dev(s);
+    CamDev cd;
+    cd.c = F3{cam->center[0], cam->center[1], cam->center[2]};
+    cd.U = F3{cam->U[0], cam->U[1], cam->U[2]};
+    cd.V = F3{cam->V[0], cam->V[1], cam->V[2]};
+    cd.W = F3{cam->W[0], cam->W[1], cam->W[2]};
+    const F3 bg = F3{fp->background[0], fp->background[1], fp->background[2]};
+
+    const uint32_t tiles = div_up(W, 8) * div_up(H, 4);
+    const uint32_t pix_blocks = div_up(tiles * 32u, 128u);
+    RT_CUDA(ctx, prof_mark(s, st));
+    k_primary<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, s->phit.p, out->prim_id, reinterpret_cast<float4 *>(out->albedo),
+                                          reinterpret_cast<float4 *>(out->normal));
+    RT_CUDA(ctx, prof_mark(s, st));
+    s->launches += 1;
+
+    if (spp) {
+        // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 64)
+        const bool base_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
+        const bool cont_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
+                             s->rng_cur_off == (uint64_t)fp->sample_offset;
+        if (!cont_ok) {
+            if (!base_ok) {
+                k_rng_init<<<div_up(npix, 128), 128, 0, st>>>(s->rng_base.p, npix, fp->seed,
+                                                              (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
+                s->launches += 1;
+                s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;
+                s->rng_valid = true;
+            }
+            RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        }
+        const uint32_t bounce_grid = (uint32_t)ctx->sm_count * 16u;
+        uint32_t done = 0;
+        for (uint32_t b = 0; b < n_batches; b++) {
+            const uint32_t S = std::min(Sb, spp - done);
+            uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
+            k_shade_primary<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p);
+            s->launches += 1;
+            for (uint32_t d = 2; d <= D; d++) {
+                RT_CUDA(ctx, prof_mark(s, st));
+                k_bounce<<<bounce_grid, 128, 0, st>>>(sd, make_queue(s, d & 1), cnt + d, make_queue(s, (d + 1) & 1), cnt + d + 1,
+                                                      s->result.p, d, D, bg);
+                RT_CUDA(ctx, prof_mark(s, st));
+                s->launches += 1;
+            }
+            const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
+            k_accumulate<<<div_up(npix, 256), 256, 0, st>>>(s->result.p, S, npix, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+            s->launches += 1;
+            done += S;
+        }
+        s->rng_cur_off = (uint64_t)fp->sample_offset + spp;
+    }
+    k_tally<<<1, 32, 0, st>>>(s->counters.p, (uint32_t)n_cnt, npix, s->seg_total.p);
+    s->launches += 1;
+    RT_CUDA(ctx, cudaEventRecord(s->ev[3], st));
+    RT_CUDA(ctx, cudaGetLastError());
+    s->have_render_ev = true;
+    s->last_stream = st;
+    s->last_primary = npix;
+    s->last_n_cnt = n_cnt;
+    return RT_OK;
+}
+
+int resolve(Context *ctx, const float *accum, size_t n, float *color, uint8_t *rgba8, cudaStream_t st) {
+    if (!n) return RT_OK;
+    k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(accum), n,
+                                                         reinterpret_cast<float4 *>(color), reinterpret_cast<uchar4 *>(rgba8));
+    RT_CUDA(ctx, cudaGetLastError());
+    return RT_OK;
+}
+
+int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_trace_rays before rt_accel_build");
+    if (!n) return RT_OK;
+    // parent_leaf is free after the build: reuse it as the gid -> slot map
+    if (skip && s->n_prims) {
+        k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(s->slot_prim.p, s->n_prims, s->vals[1].p);
+        s->launches += 1;
+    }
+    k_trace_rays<<<div_up((uint32_t)n, 128), 128, 0, st>>>(scene_dev(s), rays, skip, s->vals[1].p, (uint32_t)n, t, id);
+    s->launches += 1;
+    RT_CUDA(ctx, cudaGetLastError());
+    s->last_stream = st;
+    return RT_OK;
+}
+
+}  // namespace rtb

@@ -1,0 +1,148 @@
+"""The CPU oracle pinned against (a) cuRAND's own header / known values, (b) the reference's
+randomSpaceVector compiled from /root/reference, (c) its own committed golden renders, and checked
+for internal consistency (BVH path == brute force, determinism, partition independence)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import scenes
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+G = json.load(open(os.path.join(HERE, "golden", "ref_host_math.json")))
+IMG = np.load(os.path.join(HERE, "golden", "oracle_images.npz"))
+
+
+def test_xorwow_known_values(oracle):
+    # curand_init(1234 ^ tid, tid, 0) first two uniforms for tid 0 / 1 / 12345
+    want = {0: (0.145467639, 0.434898734), 1: (0.945122302, 0.156728163), 12345: (0.131026685, 0.840638518)}
+    for tid, (a, b) in want.items():
+        u = oracle.xorwow_uniforms(1234 ^ tid, tid, 0, 2)
+        assert "%.9f" % u[0] == "%.9f" % a and "%.9f" % u[1] == "%.9f" % b
+
+
+def test_xorwow_offset_is_sequential_consumption(oracle):
+    a = oracle.xorwow_uniforms(42, 7, 0, 200)
+    b = oracle.xorwow_uniforms(42, 7, 128, 72)
+    assert np.array_equal(a[128:], b)
+
+
+def xorwow_step(s):
+    """numpy restatement of curand() on (d, v0..v4) — the register generator of the CUDA path."""
+    d, v = int(s[0]), [int(x) for x in s[1:]]
+    t = v[0] ^ (v[0] >> 2)
+    v = v[1:] + [(v[4] ^ ((v[4] << 4) & 0xFFFFFFFF)) ^ (t ^ ((t << 1) & 0xFFFFFFFF))]
+    d = (d + 362437) & 0xFFFFFFFF
+    return np.array([d] + v, np.uint32), (v[4] + d) & 0xFFFFFFFF
+
+
+def test_register_xorwow_restatement(oracle):
+    s = oracle.xorwow_state(99, 1234, 64)
+    want = oracle.xorwow_uniforms(99, 1234, 64, 16)
+    for i in range(16):
+        s, x = xorwow_step(s)
+        u = np.float32(np.float32(x) * np.float32(2.3283064e-10) + np.float32(2.3283064e-10 / 2.0))
+        assert u == want[i]
+
+
+@pytest.mark.parametrize("case", G["rsv"])
+def test_random_space_vector_matches_reference(oracle, case):
+    """randomSpaceVector (DeviceFunctions.cuh:570-582) compiled from the reference vs our restatement:
+    identical draws; the normalisation differs by the documented rsqrtf -> 1/sqrt substitution only on
+    the device, and the host-compiled reference rsqrtf is (float)(1/sqrt((double)x)); ours is fp32
+    1/sqrt (sqrt, div, mul = three roundings), so allow the documented 2 ulp."""
+    u = oracle.xorwow_uniforms(case["seed"], case["subsequence"], case["offset"], 12).reshape(4, 3)
+    v = np.float32(-1.0) + np.float32(2.0) * u
+    l2 = (v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]) + v[:, 2] * v[:, 2]
+    mine = v * (np.float32(1.0) / np.sqrt(l2))[:, None]
+    want = np.asarray(case["out"], np.float32)
+    assert np.all(np.abs(mine.view(np.int32).astype(np.int64) - want.view(np.int32).astype(np.int64)) <= 2)
+
+
+def test_golden_render_config1(pkg, oracle, built_lib):
+    d = scenes.config1_scene(pkg)
+    r = oracle.render(scenes.flatten_world(d), scenes.config_camera(pkg, "VK"), 240, 135, 2, 5, 1234)
+    assert np.array_equal(r["prim_id"], IMG["c1_prim_id"])
+    assert np.array_equal(r["accum"].view(np.uint32), IMG["c1_accum"].view(np.uint32))
+
+
+def test_golden_render_random_scene(pkg, synth, oracle, built_lib):
+    d = scenes.random_scene(pkg, synth, 300, n_tris=40, seed=3, metal_every=5, fuzz=0.2, with_ground=True)
+    cam = pkg.camera_configure([2.2, 0.3, 0.4], [0, 0, 0], [0, 0, 1], False)
+    w = scenes.flatten_world(d)
+    r = oracle.render(w, cam, 96, 64, 3, 6, 99)
+    assert np.array_equal(r["prim_id"], IMG["rnd_prim_id"])
+    assert np.array_equal(r["accum"].view(np.uint32), IMG["rnd_accum"].view(np.uint32))
+    assert r["segments"] == int(IMG["rnd_segments"][0])
+    # the oracle's BVH path must equal its brute-force path bit for bit
+    r2 = oracle.render(w, cam, 96, 64, 3, 6, 99, accel=1)
+    assert np.array_equal(r2["prim_id"], r["prim_id"])
+    assert np.array_equal(r2["accum"].view(np.uint32), r["accum"].view(np.uint32))
+    assert r2["segments"] == r["segments"]
+
+
+def test_oracle_bvh_equals_brute_force_on_random_rays(pkg, synth, oracle, built_lib):
+    d = scenes.random_scene(pkg, synth, 5000, n_tris=500, seed=11, with_ground=True)
+    w = scenes.flatten_world(d)
+    rng = np.random.default_rng(3)
+    n = 4000
+    o = rng.uniform(-0.6, 0.6, (n, 3)).astype(np.float32)
+    dd = rng.normal(size=(n, 3)).astype(np.float32)
+    dd[:50, 0] = 0.0  # axis-parallel components
+    dd[50:100, 1:] = 0.0
+    rays = np.concatenate([o, np.full((n, 1), 1e-6, np.float32), dd, np.full((n, 1), 1e16, np.float32)], 1)
+    t0, i0 = oracle.trace(w, rays, accel=0)
+    t1, i1 = oracle.trace(w, rays, accel=1)
+    assert np.array_equal(i0, i1) and np.array_equal(t0.view(np.uint32), t1.view(np.uint32))
+    assert (i0 != 0xFFFFFFFF).mean() > 0.5
+
+
+def test_sample_partition_independence(pkg, synth, oracle, built_lib):
+    """stream(p, s) = curand_init(seed, p, (offset+s)*64): rendering samples [0,4) equals rendering
+    [0,2) and [2,4) separately and adding — the property the multi-GPU spp split relies on."""
+    d = scenes.random_scene(pkg, synth, 200, seed=5)
+    w = scenes.flatten_world(d)
+    cam = pkg.camera_configure([2.2, 0, 0], [0, 0, 0], [0, 0, 1], False)
+    full = oracle.render(w, cam, 48, 32, 4, 5, 7)["accum"]
+    a = oracle.render(w, cam, 48, 32, 2, 5, 7, sample_offset=0)["accum"]
+    b = oracle.render(w, cam, 48, 32, 2, 5, 7, sample_offset=2)["accum"]
+    assert np.allclose(a + b, full, rtol=0, atol=1e-6)
+    assert not np.array_equal(a, b)
+
+
+def test_depth_semantics(pkg, synth, oracle, built_lib):
+    """Shader.cu:102-107: a hit at depth >= max_depth contributes 0; a miss returns the background."""
+    d = scenes.random_scene(pkg, synth, 100, seed=2, with_walls=False)
+    w = scenes.flatten_world(d)
+    cam = pkg.camera_configure([2.2, 0, 0], [0, 0, 0], [0, 0, 1], False)
+    r = oracle.render(w, cam, 64, 48, 1, 1, 3, background=(0.7, 0.8, 0.9))
+    hit = r["prim_id"] != 0xFFFFFFFF
+    assert hit.any() and (~hit).any()
+    assert np.all(r["accum"][hit, :3] == 0)
+    assert np.array_equal(r["accum"][~hit, :3], np.tile(np.float32([0.7, 0.8, 0.9]), ((~hit).sum(), 1)))
+    assert r["segments"] == 64 * 48
+    assert np.all(r["albedo"][hit, 3] == 1) and np.all(r["albedo"][~hit] == 0)
+    nn = np.linalg.norm(r["normal"][hit, :3], axis=1)
+    assert np.allclose(nn, 1, atol=1e-5)
+
+
+def test_flatten_matches_oracle_xform(pkg, oracle, built_lib):
+    rng = np.random.default_rng(0)
+    m = np.asarray(pkg.construct_transform([0.3, -0.1, 0.2], [15, 40, -70], [2, 2, 2]), np.float32)
+    p = rng.uniform(-1, 1, (20, 3)).astype(np.float32)
+    got = scenes._xform_points(m, p)
+    nn = scenes._xform_normals(m, p)
+    for i in range(20):
+        assert np.array_equal(np.float32(oracle.xform_point(m, p[i])), got[i])
+        assert np.array_equal(np.float32(oracle.xform_normal(m, p[i])), nn[i])
+    s = oracle.xform_sphere(m, p[0], 0.05)
+    assert abs(s[3] - 0.1) < 1e-6
+
+
+def test_morton30(oracle):
+    assert oracle.morton30(0, 0, 0) == 0
+    assert oracle.morton30(1, 1, 1) == 0x3FFFFFFF
+    assert oracle.morton30(1.0 / 1024 + 1e-6, 0, 0) == 4
+    assert oracle.morton30(0, 1.0 / 1024 + 1e-6, 0) == 2
+    assert oracle.morton30(0, 0, 1.0 / 1024 + 1e-6) == 1
