@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--leaf-max", type=int, default=0)
     ap.add_argument("--batch-spp", type=int, default=0)
+    ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
     return ap.parse_args()
 
 
@@ -224,6 +225,9 @@ def run_ours(a):
         sc.set_option("leaf_max", a.leaf_max)
     if a.batch_spp:
         sc.set_option("batch_spp", a.batch_spp)
+    for kv in a.opt:
+        k, v = kv.split("=")
+        sc.set_option(k, int(v))
     sc.set_option("profile", 1)
     sc.set_materials(host["roughs"].ctypes.data, len(host["roughs"]), host["metals"].ctypes.data, len(host["metals"]))
     g_s = sc.add_spheres(d_centers.data_ptr(), d_radii.data_ptr(), n)

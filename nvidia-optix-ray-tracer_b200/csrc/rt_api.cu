@@ -119,6 +119,10 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     if (k == "profile") s.profile = value != 0;
     else if (k == "leaf_max") { s.leaf_max = (uint32_t)std::min<int64_t>(8, std::max<int64_t>(1, value)); s.built = false; }
     else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(1, value));
+    else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
+    else if (k == "t2") s.t2 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
+    else if (k == "fetch_min") s.fetch_min = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));
+    else if (k == "extend_blocks_per_sm") s.extend_blocks_per_sm = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));
     else return set_error(s.ctx, RT_ERR_INVALID, "unknown option '%s'", name);
     return RT_OK;
 }
@@ -136,7 +140,7 @@ int rt_scene_destroy(rt_scene scene) {
     }
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();
-    s.phit.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
+    s.phit.release(); s.hit.release(); s.u_skip.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);

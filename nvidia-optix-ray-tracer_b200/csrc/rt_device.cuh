@@ -162,78 +162,167 @@ __device__ __forceinline__ void test_slot(const SceneDev &sc, const Ray &r, floa
 
 #define RT_STACK 64
 
-// Closest hit through the LBVH.  Boxes were padded at build time and the far bound is widened by
-// 2e-6 relative, so no valid hit can be culled: the result equals brute force over all prims.
-__device__ __forceinline__ Hit trace(const SceneDev &sc, const Ray &r, uint32_t skip_slot) {
-    Hit best;
-    best.t = r.tmax;
-    best.slot = kNoSlot;
-    best.u = best.v = 0.0f;
-    const float a = dot(r.d, r.d);
-    const float inv_a = 1.0f / a;
+// ------------------------------------------------------------------ warp-cooperative closest hit
+// One lane = one ray, but the 32 lanes of a warp move through the tree in two warp-uniform phases
+// (Aila & Laine 2009 "while-while" with postponed leaves):
+//   phase 1: lanes that hold an internal node visit it (one 64-byte node = both child boxes); the
+//            first leaf a lane meets is postponed and the lane keeps descending speculatively;
+//   phase 2: lanes that hold a postponed leaf test its primitives, one primitive per iteration.
+// A phase is left when fewer than t1 / t2 lanes still want it and other lanes have work of the
+// other kind.  Finished lanes are refilled from a global ray counter (dynamic fetch) once at least
+// `fetch_min` lanes are idle, so a long ray does not hold 31 idle lanes.
+// The result is independent of all three thresholds: boxes are conservative and ties are resolved
+// by (t, global primitive id), i.e. it equals brute force over all primitives.
+constexpr int kSent = 0x7FFFFFFF;  // "no node": stack empty
+__device__ __forceinline__ bool is_internal(int n) { return (uint32_t)n < 0x7FFFFFFFu; }
 
+struct ExtendIn {
+    const float4 *o;       // path queue: origin.xyz, bits(path id)   | user rays: origin.xyz, tmin
+    const float4 *d;       // path queue: dir.xyz, bits(skip slot)    | user rays: dir.xyz, tmax
+    const uint32_t *skip;  // NULL = path queue layout, else user-ray layout with skip slot per ray
+};
+
+__device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
+                                            float4 *__restrict__ hits, int t1, int t2, int fetch_min) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    const float4 *nodes = reinterpret_cast<const float4 *>(sc.nodes);
     const BuildInfo *info = sc.info;
     const uint32_t n_huge = info->n_huge;
-    for (uint32_t i = 0; i < n_huge; i++) test_slot(sc, r, a, inv_a, info->huge_slot[i], skip_slot, best);
-    if (info->n_bvh == 0) {
-        if (best.slot == kNoSlot) best.t = RT_INF;
-        return best;
-    }
-
-    // reciprocal direction, clamped so that 0 * inf never appears
-    const float ex = fabsf(r.d.x) < 1e-30f ? copysignf(1e-30f, r.d.x) : r.d.x;
-    const float ey = fabsf(r.d.y) < 1e-30f ? copysignf(1e-30f, r.d.y) : r.d.y;
-    const float ez = fabsf(r.d.z) < 1e-30f ? copysignf(1e-30f, r.d.z) : r.d.z;
-    const float ix = 1.0f / ex, iy = 1.0f / ey, iz = 1.0f / ez;
-    const float ox = -r.o.x * ix, oy = -r.o.y * iy, oz = -r.o.z * iz;
+    const bool have_tree = info->n_bvh != 0;
 
     int stack[RT_STACK];
-    int sp = 0;
-    int node = 0;
-    const float4 *nodes = reinterpret_cast<const float4 *>(sc.nodes);
+    int sp = 0, node = kSent, leaf = 0;
+    uint32_t li = 0, idx = 0, skip_slot = kNoSlot;
+    Ray r;
+    r.o = r.d = f3(0, 0, 0);
+    r.tmin = RT_ZERO;
+    r.tmax = RT_INF;
+    Hit best;
+    best.t = 0.0f;
+    best.slot = kNoSlot;
+    best.u = best.v = 0.0f;
+    float a = 1.0f, inv_a = 1.0f, ix = 0, iy = 0, iz = 0, ox = 0, oy = 0, oz = 0;
+    bool alive = false, exhausted = false;
 
-    while (true) {
-        if (node >= 0) {
-            const float4 n0 = ldg4(nodes + 4 * (size_t)node);
-            const float4 n1 = ldg4(nodes + 4 * (size_t)node + 1);
-            const float4 n2 = ldg4(nodes + 4 * (size_t)node + 2);
-            const float4 n3 = ldg4(nodes + 4 * (size_t)node + 3);
-            const float c0x0 = __fmaf_rn(n0.x, ix, ox), c0x1 = __fmaf_rn(n0.y, ix, ox);
-            const float c0y0 = __fmaf_rn(n0.z, iy, oy), c0y1 = __fmaf_rn(n0.w, iy, oy);
-            const float c0z0 = __fmaf_rn(n2.x, iz, oz), c0z1 = __fmaf_rn(n2.y, iz, oz);
-            const float c1x0 = __fmaf_rn(n1.x, ix, ox), c1x1 = __fmaf_rn(n1.y, ix, ox);
-            const float c1y0 = __fmaf_rn(n1.z, iy, oy), c1y1 = __fmaf_rn(n1.w, iy, oy);
-            const float c1z0 = __fmaf_rn(n2.z, iz, oz), c1z1 = __fmaf_rn(n2.w, iz, oz);
-            const float lo0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), r.tmin));
-            const float hi0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
-            const float lo1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), r.tmin));
-            const float hi1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
-            const bool h0 = lo0 <= hi0 * 1.000002f;
-            const bool h1 = lo1 <= hi1 * 1.000002f;
-            const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
-            if (h0 && h1) {
-                const bool swap = lo1 < lo0;
-                node = swap ? ch1 : ch0;
-                if (sp < RT_STACK) stack[sp++] = swap ? ch0 : ch1;
-            } else if (h0) {
-                node = ch0;
-            } else if (h1) {
-                node = ch1;
-            } else {
-                if (sp == 0) break;
-                node = stack[--sp];
+    for (;;) {
+        // ---- dynamic fetch
+        const uint32_t dead = __ballot_sync(FULL, !alive);
+        if (dead && !exhausted && (dead == FULL || __popc(dead) >= fetch_min)) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(fetch_ctr, (uint32_t)__popc(dead));
+            base = __shfl_sync(FULL, base, 0);
+            if (base + __popc(dead) >= n) exhausted = true;
+            const uint32_t i = base + __popc(dead & lt);
+            if (!alive && i < n) {
+                const float4 o4 = in.o[i], d4 = in.d[i];
+                idx = i;
+                r.o = f3(o4.x, o4.y, o4.z);
+                r.d = f3(d4.x, d4.y, d4.z);
+                if (in.skip) {
+                    r.tmin = o4.w;
+                    r.tmax = d4.w;
+                    skip_slot = in.skip[i];
+                } else {
+                    r.tmin = RT_ZERO;  // Shader.cu:231-233, 264-267
+                    r.tmax = RT_INF;
+                    skip_slot = __float_as_uint(d4.w);
+                }
+                best.t = r.tmax;
+                best.slot = kNoSlot;
+                best.u = best.v = 0.0f;
+                a = dot(r.d, r.d);
+                inv_a = 1.0f / a;
+                for (uint32_t k = 0; k < n_huge; k++) test_slot(sc, r, a, inv_a, info->huge_slot[k], skip_slot, best);
+                // reciprocal direction, clamped so that 0 * inf never appears
+                const float ex = fabsf(r.d.x) < 1e-30f ? copysignf(1e-30f, r.d.x) : r.d.x;
+                const float ey = fabsf(r.d.y) < 1e-30f ? copysignf(1e-30f, r.d.y) : r.d.y;
+                const float ez = fabsf(r.d.z) < 1e-30f ? copysignf(1e-30f, r.d.z) : r.d.z;
+                ix = 1.0f / ex; iy = 1.0f / ey; iz = 1.0f / ez;
+                ox = -r.o.x * ix; oy = -r.o.y * iy; oz = -r.o.z * iz;
+                sp = 0;
+                leaf = 0;
+                li = 0;
+                node = have_tree ? 0 : kSent;
+                alive = true;
             }
-        } else {
-            const uint32_t enc = (uint32_t)node;
-            const uint32_t first = enc & kLeafFirstMask;
-            const uint32_t cnt = ((enc >> kLeafCountShift) & 7u) + 1u;
-            for (uint32_t i = 0; i < cnt; i++) test_slot(sc, r, a, inv_a, first + i, skip_slot, best);
-            if (sp == 0) break;
-            node = stack[--sp];
+        }
+        if (!__any_sync(FULL, alive)) break;
+
+        // ---- phase 1: internal nodes
+        bool first = true;
+        for (;;) {
+            const bool want = alive && is_internal(node);
+            const uint32_t mw = __ballot_sync(FULL, want);
+            if (!mw) break;
+            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && leaf != 0)) break;
+            first = false;
+            if (want) {
+                const float4 n0 = ldg4(nodes + 4 * (size_t)node);
+                const float4 n1 = ldg4(nodes + 4 * (size_t)node + 1);
+                const float4 n2 = ldg4(nodes + 4 * (size_t)node + 2);
+                const float2 n3 = __ldg(reinterpret_cast<const float2 *>(nodes + 4 * (size_t)node + 3));
+                const float c0x0 = __fmaf_rn(n0.x, ix, ox), c0x1 = __fmaf_rn(n0.y, ix, ox);
+                const float c0y0 = __fmaf_rn(n0.z, iy, oy), c0y1 = __fmaf_rn(n0.w, iy, oy);
+                const float c0z0 = __fmaf_rn(n2.x, iz, oz), c0z1 = __fmaf_rn(n2.y, iz, oz);
+                const float c1x0 = __fmaf_rn(n1.x, ix, ox), c1x1 = __fmaf_rn(n1.y, ix, ox);
+                const float c1y0 = __fmaf_rn(n1.z, iy, oy), c1y1 = __fmaf_rn(n1.w, iy, oy);
+                const float c1z0 = __fmaf_rn(n2.z, iz, oz), c1z1 = __fmaf_rn(n2.w, iz, oz);
+                const float lo0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), r.tmin));
+                const float hi0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
+                const float lo1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), r.tmin));
+                const float hi1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
+                const bool h0 = lo0 <= hi0 * 1.000002f;
+                const bool h1 = lo1 <= hi1 * 1.000002f;
+                const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
+                if (h0 && h1) {
+                    const bool swap = lo1 < lo0;
+                    node = swap ? ch1 : ch0;
+                    stack[sp++] = swap ? ch0 : ch1;  // depth <= 62 < RT_STACK (30 key bits + 32 index bits)
+                } else if (h0) {
+                    node = ch0;
+                } else if (h1) {
+                    node = ch1;
+                } else {
+                    node = sp ? stack[--sp] : kSent;
+                }
+                if (node < 0 && leaf == 0) {  // postpone the first leaf, keep descending
+                    leaf = node;
+                    node = sp ? stack[--sp] : kSent;
+                }
+            }
+        }
+
+        // ---- phase 2: postponed leaves, one primitive per iteration
+        first = true;
+        for (;;) {
+            const bool hl = alive && leaf != 0;
+            const uint32_t ml = __ballot_sync(FULL, hl);
+            if (!ml) break;
+            if (!first && __popc(ml) < t2 && __any_sync(FULL, alive && is_internal(node))) break;
+            first = false;
+            if (hl) {
+                const uint32_t enc = (uint32_t)leaf;
+                const uint32_t cnt = ((enc >> kLeafCountShift) & 7u) + 1u;
+                test_slot(sc, r, a, inv_a, (enc & kLeafFirstMask) + li, skip_slot, best);
+                if (++li == cnt) {
+                    li = 0;
+                    leaf = 0;
+                    if (node < 0) {
+                        leaf = node;
+                        node = sp ? stack[--sp] : kSent;
+                    }
+                }
+            }
+        }
+
+        // ---- retire finished rays
+        if (alive && node == kSent && leaf == 0) {
+            hits[idx] = make_float4(best.slot == kNoSlot ? RT_INF : best.t, __uint_as_float(best.slot), best.u, best.v);
+            alive = false;
         }
     }
-    if (best.slot == kNoSlot) best.t = RT_INF;
-    return best;
 }
 
 }  // namespace rtb

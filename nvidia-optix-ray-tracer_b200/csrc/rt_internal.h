@@ -161,6 +161,10 @@ struct Scene {
     DevBuf<uint4> q_r[2];
     DevBuf<uint32_t> q_r4[2];
     DevBuf<float4> result;        // per path
+    DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
+    DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
+    uint32_t t1 = 12, t2 = 12, fetch_min = 12;  // traversal thresholds (see extend_warp)
+    uint32_t extend_blocks_per_sm = 8;
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;
 

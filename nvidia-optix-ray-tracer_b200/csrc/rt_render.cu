@@ -137,22 +137,46 @@ __device__ __forceinline__ void queue_write(const Queue &q, uint32_t i, F3 o, F3
     q.r4[i] = r.v4;
 }
 
-// ------------------------------------------------------------------ primary visibility (one ray per pixel)
+// ------------------------------------------------------------------ closest hit for a ray buffer (persistent warps)
+__global__ void __launch_bounds__(128, 8)
+k_extend(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t n_fixed, uint32_t *fetch_ctr,
+         float4 *__restrict__ hits, int t1, int t2, int fetch_min) {
+    const uint32_t n = n_ptr ? *n_ptr : n_fixed;
+    extend_warp(sc, in, n, fetch_ctr, hits, t1, t2, fetch_min);
+}
+
+// ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
+// One ray per pixel, written in pixel order into the path-queue layout (path id = pixel, no skip).
 __global__ void __launch_bounds__(128)
-k_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, float4 *__restrict__ phit, uint32_t *__restrict__ prim_id,
-          float4 *__restrict__ albedo, float4 *__restrict__ normal) {
+k_raygen(CamDev cam, uint32_t W, uint32_t H, float4 *__restrict__ qo, float4 *__restrict__ qd) {
     uint32_t x, y;
     if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y)) return;
-    const size_t p = (size_t)y * W + x;  // Shader.cu:270
+    const uint32_t p = y * W + x;  // Shader.cu:270
     const Ray r = primary_ray(cam, x, y, W, H);
-    const Hit h = trace(sc, r, kNoSlot);
-    phit[p] = make_float4(h.t, __uint_as_float(h.slot), h.u, h.v);
+    qo[p] = make_float4(r.o.x, r.o.y, r.o.z, __uint_as_float(p));
+    qd[p] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(kNoSlot));
+}
+
+// primary-hit ids and first-hit AOVs (Shader.cu:216-227, 284-286)
+__global__ void __launch_bounds__(128)
+k_primary_aov(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, const float4 *__restrict__ phit,
+              uint32_t *__restrict__ prim_id, float4 *__restrict__ albedo, float4 *__restrict__ normal) {
+    uint32_t x, y;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y)) return;
+    const size_t p = (size_t)y * W + x;
+    const float4 hh = phit[p];
+    Hit h;
+    h.t = hh.x;
+    h.slot = __float_as_uint(hh.y);
+    h.u = hh.z;
+    h.v = hh.w;
     if (prim_id) prim_id[p] = (h.slot == kNoSlot) ? RT_MISS_ID : __ldg(sc.slot_prim + h.slot);
     if (albedo || normal) {
         float4 a = make_float4(0, 0, 0, 0), n = make_float4(0, 0, 0, 0);  // Shader.cu:284-286
         if (h.slot != kNoSlot) {
-            // first-hit AOVs, Shader.cu:216-227 (never consumes RNG: fuzz/rough draws excluded)
+            // first-hit AOVs never consume RNG (fuzz/rough draws excluded)
             Rng dummy = {0, 1, 2, 3, 4, 5};
+            const Ray r = primary_ray(cam, x, y, W, H);
             const Scatter s = scatter(sc, r, h, dummy);
             const F3 nn = normalize3(s.N);
             a = make_float4(s.alb.x, s.alb.y, s.alb.z, 1.0f);
@@ -206,7 +230,7 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
             // miss: 1 * background (Shader.cu:276-287); depth cut-off: 0 (:102-107)
             result[pid] = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
         }
-        if (valid) {
+        if (valid) {  // every pixel's stream advances (a pixel that misses now may hit after the next rebuild)
 #pragma unroll 8
             for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
         }
@@ -221,10 +245,12 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
     }
 }
 
-// ------------------------------------------------------------------ one bounce over the ray queue (persistent)
-__global__ void __launch_bounds__(128)
-k_bounce(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, Queue out, uint32_t *out_count,
-         float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg) {
+// ------------------------------------------------------------------ closest-hit / miss programs over the ray queue
+// One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
+// state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
+__global__ void __launch_bounds__(256)
+k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
+        uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg) {
     const uint32_t n = *in_count;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; w0 < n; w0 += stride) {
@@ -236,7 +262,7 @@ k_bounce(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, Queue out
         F3 thr;
         uint32_t pid = 0, slot = kNoSlot;
         if (valid) {
-            const float4 o = in.o[i], d = in.d[i], t = in.t[i];
+            const float4 o = in.o[i], d = in.d[i], t = in.t[i], hh = hits[i];
             Ray ray;
             ray.o = f3(o.x, o.y, o.z);
             ray.d = f3(d.x, d.y, d.z);
@@ -244,7 +270,11 @@ k_bounce(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, Queue out
             ray.tmax = RT_INF;
             pid = __float_as_uint(o.w);
             thr = f3(t.x, t.y, t.z);
-            const Hit h = trace(sc, ray, __float_as_uint(d.w));
+            Hit h;
+            h.t = hh.x;
+            h.slot = __float_as_uint(hh.y);
+            h.u = hh.z;
+            h.v = hh.w;
             if (h.slot == kNoSlot) {
                 result[pid] = make_float4(thr.x * bg.x, thr.y * bg.y, thr.z * bg.z, 0.0f);
             } else if (depth >= max_depth) {
@@ -305,20 +335,25 @@ k_resolve(const float4 *__restrict__ accum, size_t n, float4 *__restrict__ color
 
 // ------------------------------------------------------------------ validation: caller-supplied rays
 __global__ void __launch_bounds__(128)
-k_trace_rays(SceneDev sc, const float *__restrict__ rays, const uint32_t *__restrict__ skip_gid,
-             const uint32_t *__restrict__ gid_to_slot, uint32_t n, float *__restrict__ out_t, uint32_t *__restrict__ out_id) {
+k_pack_rays(const float *__restrict__ rays, const uint32_t *__restrict__ skip_gid, const uint32_t *__restrict__ gid_to_slot,
+            uint32_t n, float4 *__restrict__ qo, float4 *__restrict__ qd, uint32_t *__restrict__ qskip) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Ray r;
-    r.o = f3(rays[8 * (size_t)i], rays[8 * (size_t)i + 1], rays[8 * (size_t)i + 2]);
-    r.tmin = rays[8 * (size_t)i + 3];
-    r.d = f3(rays[8 * (size_t)i + 4], rays[8 * (size_t)i + 5], rays[8 * (size_t)i + 6]);
-    r.tmax = rays[8 * (size_t)i + 7];
+    const float *r = rays + 8 * (size_t)i;
+    qo[i] = make_float4(r[0], r[1], r[2], r[3]);
+    qd[i] = make_float4(r[4], r[5], r[6], r[7]);
     uint32_t skip = kNoSlot;
     if (skip_gid && skip_gid[i] != RT_MISS_ID) skip = gid_to_slot[skip_gid[i]];
-    const Hit h = trace(sc, r, skip);
-    out_t[i] = (h.slot == kNoSlot) ? __int_as_float(0x7F800000) : h.t;
-    out_id[i] = (h.slot == kNoSlot) ? RT_MISS_ID : sc.slot_prim[h.slot];
+    qskip[i] = skip;
+}
+__global__ void __launch_bounds__(128)
+k_unpack_hits(SceneDev sc, const float4 *__restrict__ hits, uint32_t n, float *__restrict__ out_t, uint32_t *__restrict__ out_id) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = hits[i];
+    const uint32_t slot = __float_as_uint(h.y);
+    out_t[i] = (slot == kNoSlot) ? __int_as_float(0x7F800000) : h.x;
+    out_id[i] = (slot == kNoSlot) ? RT_MISS_ID : sc.slot_prim[slot];
 }
 __global__ void k_invert_slots(const uint32_t *__restrict__ slot_prim, uint32_t n, uint32_t *__restrict__ gid_to_slot) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -350,6 +385,19 @@ static cudaError_t prof_mark(Scene *s, cudaStream_t st) {
 
 static Queue make_queue(Scene *s, int k) { return Queue{s->q_o[k].p, s->q_d[k].p, s->q_t[k].p, s->q_r[k].p, s->q_r4[k].p}; }
 
+// one closest-hit pass over a ray buffer; timed when option "profile" is on
+static int launch_extend(Scene *s, const SceneDev &sd, const ExtendIn &in, const uint32_t *n_ptr, uint32_t n_fixed,
+                         uint32_t *fetch_ctr, float4 *hits, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    uint32_t grid = (uint32_t)ctx->sm_count * s->extend_blocks_per_sm;
+    if (!n_ptr) grid = std::min(grid, std::max(1u, div_up(n_fixed, 128u)));
+    RT_CUDA(ctx, prof_mark(s, st));
+    k_extend<<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min);
+    RT_CUDA(ctx, prof_mark(s, st));
+    s->launches += 1;
+    return RT_OK;
+}
+
 int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, const rt_outputs *out, cudaStream_t st) {
     Context *ctx = s->ctx;
     if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_render before rt_accel_build");
@@ -366,21 +414,27 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     const uint32_t D = fp->max_depth;
 
     RT_CUDA(ctx, s->phit.reserve(npix, &s->bytes));
+    const size_t qn = std::max((size_t)npix, spp ? (size_t)npix * std::min(Sb, spp) : (size_t)0);
+    for (int k = 0; k < 2; k++) {
+        const size_t qk = (k == 0 || spp) ? qn : 1;  // primary rays use queue 0's origin/direction arrays
+        RT_CUDA(ctx, s->q_o[k].reserve(qk, &s->bytes));
+        RT_CUDA(ctx, s->q_d[k].reserve(qk, &s->bytes));
+    }
     if (spp) {
         RT_CUDA(ctx, s->rng_base.reserve(6 * (size_t)npix, &s->bytes));
         RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
-        const size_t qn = (size_t)npix * std::min(Sb, spp);
         for (int k = 0; k < 2; k++) {
-            RT_CUDA(ctx, s->q_o[k].reserve(qn, &s->bytes));
-            RT_CUDA(ctx, s->q_d[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_r4[k].reserve(qn, &s->bytes));
         }
+        RT_CUDA(ctx, s->hit.reserve(qn, &s->bytes));
         RT_CUDA(ctx, s->result.reserve(qn, &s->bytes));
     }
+    // counters: [n_batches][D+3] queue sizes, then one fetch counter per k_extend launch
     const size_t n_cnt = (size_t)(n_batches ? n_batches : 1) * (D + 3);
-    RT_CUDA(ctx, s->counters.reserve(n_cnt, &s->bytes));
+    const size_t n_fetch = 1 + (size_t)n_batches * (D + 1);
+    RT_CUDA(ctx, s->counters.reserve(n_cnt + n_fetch, &s->bytes));
     if (!s->seg_total.p) {
         RT_CUDA(ctx, s->seg_total.reserve(1, &s->bytes));
         RT_CUDA(ctx, cudaMemsetAsync(s->seg_total.p, 0, sizeof(unsigned long long), st));
@@ -389,7 +443,8 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&s->ev[k]));
 
     RT_CUDA(ctx, cudaEventRecord(s->ev[2], st));
-    RT_CUDA(ctx, cudaMemsetAsync(s->counters.p, 0, n_cnt * sizeof(uint32_t), st));
+    RT_CUDA(ctx, cudaMemsetAsync(s->counters.p, 0, (n_cnt + n_fetch) * sizeof(uint32_t), st));
+    uint32_t *fetch = s->counters.p + n_cnt;
 
     const SceneDev sd = scene_dev(s);
     CamDev cd;
@@ -401,11 +456,19 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
 
     const uint32_t tiles = div_up(W, 8) * div_up(H, 4);
     const uint32_t pix_blocks = div_up(tiles * 32u, 128u);
-    RT_CUDA(ctx, prof_mark(s, st));
-    k_primary<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, s->phit.p, out->prim_id, reinterpret_cast<float4 *>(out->albedo),
-                                          reinterpret_cast<float4 *>(out->normal));
-    RT_CUDA(ctx, prof_mark(s, st));
+    // primary visibility: raygen -> closest hit -> ids / AOVs
+    k_raygen<<<pix_blocks, 128, 0, st>>>(cd, W, H, s->q_o[0].p, s->q_d[0].p);
     s->launches += 1;
+    {
+        const ExtendIn in{s->q_o[0].p, s->q_d[0].p, nullptr};
+        const int rc = launch_extend(s, sd, in, nullptr, npix, fetch++, s->phit.p, st);
+        if (rc) return rc;
+    }
+    if (out->prim_id || out->albedo || out->normal) {
+        k_primary_aov<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, s->phit.p, out->prim_id, reinterpret_cast<float4 *>(out->albedo),
+                                                  reinterpret_cast<float4 *>(out->normal));
+        s->launches += 1;
+    }
 
     if (spp) {
         // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 64)
@@ -422,7 +485,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             }
             RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
         }
-        const uint32_t bounce_grid = (uint32_t)ctx->sm_count * 16u;
+        const uint32_t shade_grid = (uint32_t)ctx->sm_count * 8u;
         uint32_t done = 0;
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
@@ -430,10 +493,11 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             k_shade_primary<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
-                RT_CUDA(ctx, prof_mark(s, st));
-                k_bounce<<<bounce_grid, 128, 0, st>>>(sd, make_queue(s, d & 1), cnt + d, make_queue(s, (d + 1) & 1), cnt + d + 1,
-                                                      s->result.p, d, D, bg);
-                RT_CUDA(ctx, prof_mark(s, st));
+                const Queue qin = make_queue(s, d & 1), qout = make_queue(s, (d + 1) & 1);
+                const ExtendIn in{qin.o, qin.d, nullptr};
+                const int rc = launch_extend(s, sd, in, cnt + d, 0, fetch++, s->hit.p, st);
+                if (rc) return rc;
+                k_shade<<<shade_grid, 256, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg);
                 s->launches += 1;
             }
             const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
@@ -466,13 +530,24 @@ int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, floa
     Context *ctx = s->ctx;
     if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_trace_rays before rt_accel_build");
     if (!n) return RT_OK;
-    // parent_leaf is free after the build: reuse it as the gid -> slot map
+    if (n >= (1ull << 31)) return set_error(ctx, RT_ERR_INVALID, "too many rays");
+    RT_CUDA(ctx, s->q_o[0].reserve(n, &s->bytes));
+    RT_CUDA(ctx, s->q_d[0].reserve(n, &s->bytes));
+    RT_CUDA(ctx, s->hit.reserve(n, &s->bytes));
+    RT_CUDA(ctx, s->u_skip.reserve(n + 1, &s->bytes));
+    // vals[1] is free after the build: reuse it as the gid -> slot map
     if (skip && s->n_prims) {
         k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(s->slot_prim.p, s->n_prims, s->vals[1].p);
         s->launches += 1;
     }
-    k_trace_rays<<<div_up((uint32_t)n, 128), 128, 0, st>>>(scene_dev(s), rays, skip, s->vals[1].p, (uint32_t)n, t, id);
-    s->launches += 1;
+    k_pack_rays<<<div_up((uint32_t)n, 128), 128, 0, st>>>(rays, skip, s->vals[1].p, (uint32_t)n, s->q_o[0].p, s->q_d[0].p, s->u_skip.p);
+    uint32_t *fetch = s->u_skip.p + n;
+    RT_CUDA(ctx, cudaMemsetAsync(fetch, 0, sizeof(uint32_t), st));
+    const ExtendIn in{s->q_o[0].p, s->q_d[0].p, s->u_skip.p};
+    const int rc = launch_extend(s, scene_dev(s), in, nullptr, (uint32_t)n, fetch, s->hit.p, st);
+    if (rc) return rc;
+    k_unpack_hits<<<div_up((uint32_t)n, 128), 128, 0, st>>>(scene_dev(s), s->hit.p, (uint32_t)n, t, id);
+    s->launches += 2;
     RT_CUDA(ctx, cudaGetLastError());
     s->last_stream = st;
     return RT_OK;
