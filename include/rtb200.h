@@ -117,8 +117,11 @@ int rt_abi_version(void);
  *      and the OptixInstance fill (RendererTime.cu:116-130, RendererMesh.cu:130-148) ---------- */
 int rt_scene_create(rt_context ctx, rt_scene *out);
 int rt_scene_destroy(rt_scene scene);
-/* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "leaf_max" (1..8
- * primitives per BVH leaf), "batch_spp" (samples per pixel in flight per wavefront batch). */
+/* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "wide" (1 = traverse
+ * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (1..8 primitives per binary
+ * leaf; capped at 3 under "wide"), "batch_spp" (samples per pixel in flight per wavefront batch),
+ * "t1" / "t2" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
+ * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel). */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 
 /* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz
@@ -170,6 +173,12 @@ int rt_get_stats(rt_scene scene, rt_stats *out); /* synchronises the scene's las
  * nodes: 16 floats per node; slot_geom: 4 floats per slot; slot_prim: u32 per slot. Any NULL. */
 int rt_accel_download(rt_scene scene, float *nodes_h, float *slot_geom_h, uint32_t *slot_prim_h,
                       uint32_t *sorted_keys_h);
+/* Same for the 8-wide compressed BVH that traversal actually walks (option "wide" = 1, the default):
+ * wnodes_h: 20 floats (80 bytes) per wide node, layout in DESIGN.md; slot arrays in the re-packed
+ * per-wide-node primitive order.  *n_wnodes_out receives the node count.  Any pointer may be NULL;
+ * capacity needed: n_prims entries each (query with all-NULL first). */
+int rt_accel_download_wide(rt_scene scene, float *wnodes_h, float *slot_geom_h, uint32_t *slot_prim_h,
+                           uint64_t *n_wnodes_out);
 /* Closest hit for caller-supplied rays through the same traversal kernel (validation):
  * dev_rays float[8*n] = o.xyz tmin d.xyz tmax; dev_skip u32[n] global prim id or RT_MISS_ID
  * (may be NULL); outputs dev_t float[n], dev_id u32[n]. */

@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "rt_scene_create", "rt_scene_destroy", "rt_scene_set_option", "rt_scene_set_materials", "rt_scene_add_spheres",
     "rt_scene_add_triangles", "rt_scene_update_group", "rt_scene_add_instance",
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
-    "rt_accel_download", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
+    "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
 ]
 
@@ -102,6 +102,7 @@ def lib() -> C.CDLL:
         L.rt_resolve.argtypes = [vp, vp, sz, vp, vp, vp]
         L.rt_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.rt_accel_download.argtypes = [vp, vp, vp, vp, vp]
+        L.rt_accel_download_wide.argtypes = [vp, vp, vp, vp, C.POINTER(u64)]
         L.rt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp, vp]
         L.rt_camera_configure.argtypes = [f_p, f_p, f_p, C.c_int, C.POINTER(Camera)]
         L.rt_camera_configure.restype = None
@@ -233,6 +234,11 @@ class Scene:
 
     def download(self, nodes_ptr=None, slot_geom_ptr=None, slot_prim_ptr=None, keys_ptr=None):
         self.ctx.check(lib().rt_accel_download(self._h, nodes_ptr, slot_geom_ptr, slot_prim_ptr, keys_ptr))
+
+    def download_wide(self, wnodes_ptr=None, slot_geom_ptr=None, slot_prim_ptr=None) -> int:
+        n = C.c_uint64()
+        self.ctx.check(lib().rt_accel_download_wide(self._h, wnodes_ptr, slot_geom_ptr, slot_prim_ptr, C.byref(n)))
+        return n.value
 
     def close(self):
         if self._h:

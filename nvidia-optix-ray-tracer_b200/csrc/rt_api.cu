@@ -119,6 +119,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     if (k == "profile") s.profile = value != 0;
     else if (k == "leaf_max") { s.leaf_max = (uint32_t)std::min<int64_t>(8, std::max<int64_t>(1, value)); s.built = false; }
     else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(1, value));
+    else if (k == "wide") { s.wide = value != 0; s.built = false; }
     else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "t2") s.t2 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "fetch_min") s.fetch_min = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));
@@ -140,6 +141,7 @@ int rt_scene_destroy(rt_scene scene) {
     }
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();
+    s.wnodes.release(); s.wslot_geom.release(); s.wslot_prim.release(); s.wslot_mat.release();
     s.phit.release(); s.hit.release(); s.u_skip.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
@@ -282,7 +284,7 @@ int rt_get_stats(rt_scene scene, rt_stats *out) {
         RT_CUDA(ctx, cudaMemcpy(&bi, s.info.p, sizeof bi, cudaMemcpyDeviceToHost));
         out->n_bvh_prims = bi.n_bvh;
         out->n_huge = bi.n_huge;
-        out->n_nodes = bi.n_bvh >= 2 ? bi.n_bvh - 1 : 1;
+        out->n_nodes = s.wide ? bi.n_wnodes : (bi.n_bvh >= 2 ? bi.n_bvh - 1 : 1);
         for (int a = 0; a < 3; a++) {
             out->scene_lo[a] = bi.scene_lo[a];
             out->scene_hi[a] = bi.scene_hi[a];
@@ -325,6 +327,24 @@ int rt_accel_download(rt_scene scene, float *nodes_h, float *slot_geom_h, uint32
         if (slot_geom_h) RT_CUDA(ctx, cudaMemcpy(slot_geom_h, s.slot_geom.p, s.n_prims * sizeof(float4), cudaMemcpyDeviceToHost));
         if (slot_prim_h) RT_CUDA(ctx, cudaMemcpy(slot_prim_h, s.slot_prim.p, s.n_prims * sizeof(uint32_t), cudaMemcpyDeviceToHost));
         if (sorted_keys_h) RT_CUDA(ctx, cudaMemcpy(sorted_keys_h, s.keys[0].p, s.n_prims * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    }
+    return RT_OK;
+}
+
+int rt_accel_download_wide(rt_scene scene, float *wnodes_h, float *slot_geom_h, uint32_t *slot_prim_h, uint64_t *n_wnodes_out) {
+    if (!scene) return RT_ERR_INVALID;
+    Scene &s = scene->s;
+    Context *ctx = s.ctx;
+    if (!s.built || !s.wide) return set_error(ctx, RT_ERR_STATE, "rt_accel_download_wide needs a built scene with option wide=1");
+    DeviceGuard g(ctx->device);
+    RT_CUDA(ctx, cudaStreamSynchronize(s.last_stream));
+    BuildInfo bi;
+    RT_CUDA(ctx, cudaMemcpy(&bi, s.info.p, sizeof bi, cudaMemcpyDeviceToHost));
+    if (n_wnodes_out) *n_wnodes_out = bi.n_wnodes;
+    if (wnodes_h && bi.n_wnodes) RT_CUDA(ctx, cudaMemcpy(wnodes_h, s.wnodes.p, (size_t)bi.n_wnodes * sizeof(WNode), cudaMemcpyDeviceToHost));
+    if (s.n_prims) {
+        if (slot_geom_h) RT_CUDA(ctx, cudaMemcpy(slot_geom_h, s.wslot_geom.p, s.n_prims * sizeof(float4), cudaMemcpyDeviceToHost));
+        if (slot_prim_h) RT_CUDA(ctx, cudaMemcpy(slot_prim_h, s.wslot_prim.p, s.n_prims * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     }
     return RT_OK;
 }

@@ -9,9 +9,14 @@
 //   (8-bit digits, 4 passes) -> gather to Morton order -> Karras hierarchy -> bottom-up refit.
 // All kernels are HBM-bound streaming passes; algorithmic bytes per primitive are listed in
 // DESIGN.md §5.
+#include <algorithm>
 #include <cfloat>
 
+#include <cooperative_groups.h>
+
 #include "rt_device.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace rtb {
 
@@ -225,6 +230,10 @@ __global__ void k_decide(const uint32_t *__restrict__ bucket_tab, uint32_t n_tot
         info->scene_hi[a] = 0.0f;
     }
     for (uint32_t i = 0; i < kMaxHuge; i++) info->huge_slot[i] = (n_total - n_huge) + i;
+    info->n_wnodes = 0;
+    info->n_wprims = 0;
+    info->level_end = 0;
+    info->pad_ = 0;
 }
 
 // ------------------------------------------------------------------ K3: 30-bit Morton keys
@@ -471,6 +480,15 @@ k_refit(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12
     }
 }
 
+// padded boxes of the outlier primitives (tested after the tree walk, culled by these boxes)
+__global__ void k_huge_boxes(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info) {
+    const uint32_t k = threadIdx.x;
+    if (k >= info->n_huge) return;
+    const Box3 b = pad_box(prim_box(slot_geom[info->n_bvh + k], tri_v12));
+    info->huge_lo[k][0] = b.lo.x; info->huge_lo[k][1] = b.lo.y; info->huge_lo[k][2] = b.lo.z;
+    info->huge_hi[k][0] = b.hi.x; info->huge_hi[k][1] = b.hi.y; info->huge_hi[k][2] = b.hi.z;
+}
+
 // n_bvh <= 1: the root is the only node
 __global__ void k_small_tree(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info, Node *nodes) {
     if (threadIdx.x || blockIdx.x) return;
@@ -494,6 +512,207 @@ __global__ void k_small_tree(const float4 *__restrict__ slot_geom, const float4 
     store_child_box(nodes, 0, b);
     store_child_box(nodes, 1, e);
     nodes[0].n3 = make_float4(__int_as_float(c0), __int_as_float(invalid), 0.0f, 0.0f);
+}
+
+// ------------------------------------------------------------------ K8: collapse to the 8-wide compressed BVH
+// Top-down, one thread per wide node, level-synchronous inside ONE cooperative kernel (grid.sync
+// between levels).  The task queue is the wide-node array itself: wtask[w] = binary node that wide
+// node w collapses.  A wide node starts from the two children of its binary node and keeps opening
+// the internal child with the largest surface area until it has 8 children or only leaves.  Leaf
+// primitives are re-packed so that every wide node's primitives are contiguous (prim_base).
+struct CChild {
+    int enc;  // binary child encoding: >= 0 internal node, < 0 leaf (first slot, count)
+    float lo[3], hi[3];
+};
+__device__ __forceinline__ void read_children(const Node *__restrict__ nodes, int b, CChild &c0, CChild &c1) {
+    const float4 *q = reinterpret_cast<const float4 *>(nodes + b);
+    const float4 n0 = q[0], n1 = q[1], n2 = q[2], n3 = q[3];
+    c0.enc = __float_as_int(n3.x);
+    c0.lo[0] = n0.x; c0.hi[0] = n0.y; c0.lo[1] = n0.z; c0.hi[1] = n0.w; c0.lo[2] = n2.x; c0.hi[2] = n2.y;
+    c1.enc = __float_as_int(n3.y);
+    c1.lo[0] = n1.x; c1.hi[0] = n1.y; c1.lo[1] = n1.z; c1.hi[1] = n1.w; c1.lo[2] = n2.z; c1.hi[2] = n2.w;
+}
+// smallest biased exponent e >= 1 with 255 * 2^(e-127) >= ext
+__device__ __forceinline__ uint32_t quant_exp(float ext) {
+    const uint32_t b = __float_as_uint(ext * (1.0f / 255.0f));
+    uint32_t e = (b >> 23) & 0xFFu;
+    if (b & 0x7FFFFFu) e += 1;
+    return min(max(e, 1u), 254u);
+}
+
+__device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict__ wtask,
+                             WNode *__restrict__ wnodes, const float4 *__restrict__ slot_geom,
+                             const uint32_t *__restrict__ slot_prim, const uint32_t *__restrict__ slot_mat,
+                             float4 *__restrict__ wslot_geom, uint32_t *__restrict__ wslot_prim, uint32_t *__restrict__ wslot_mat) {
+    CChild ch[8];
+    int cnt = 0;
+    {
+        CChild c0, c1;
+        read_children(nodes, b, c0, c1);
+        if (c0.lo[0] <= c0.hi[0]) ch[cnt++] = c0;  // the 1-primitive tree has an empty second child
+        if (c1.lo[0] <= c1.hi[0]) ch[cnt++] = c1;
+    }
+    while (cnt < 8) {
+        int bi = -1;
+        float ba = -1.0f;
+        for (int i = 0; i < cnt; i++) {
+            if (ch[i].enc >= 0) {
+                const float dx = ch[i].hi[0] - ch[i].lo[0], dy = ch[i].hi[1] - ch[i].lo[1], dz = ch[i].hi[2] - ch[i].lo[2];
+                const float ar = dx * dy + dy * dz + dz * dx;
+                if (ar > ba) {
+                    ba = ar;
+                    bi = i;
+                }
+            }
+        }
+        if (bi < 0) break;
+        CChild c0, c1;
+        read_children(nodes, ch[bi].enc, c0, c1);
+        ch[bi] = c0;
+        ch[cnt++] = c1;
+    }
+    // node box and per-axis quantisation grid
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; a++) {
+        lo[a] = ch[0].lo[a];
+        hi[a] = ch[0].hi[a];
+        for (int i = 1; i < cnt; i++) {
+            lo[a] = fminf(lo[a], ch[i].lo[a]);
+            hi[a] = fmaxf(hi[a], ch[i].hi[a]);
+        }
+    }
+    // The grid origin sits one step below the node box and every child interval is widened by one
+    // step per side: the traversal's folded FMA may move a plane by half a step (rt_device.cuh qfloat).
+    uint32_t eb[3];
+    uint8_t qlo[3][8], qhi[3][8];
+    float org[3];
+    for (int a = 0; a < 3; a++) {
+        eb[a] = quant_exp((hi[a] - lo[a]) * (255.0f / 252.0f));
+        for (;;) {
+            const float sc = __uint_as_float(eb[a] << 23);
+            org[a] = lo[a] - sc;
+            bool ok = true;
+            for (int i = 0; i < cnt; i++) {
+                // conservative: decoded lo (rounded up) <= child lo, decoded hi (rounded down) >= child hi
+                float ql = fmaxf(floorf((ch[i].lo[a] - org[a]) / sc), 0.0f);
+                if (ql > 0.0f && __fmaf_ru(ql, sc, org[a]) > ch[i].lo[a]) ql -= 1.0f;
+                float qh = fmaxf(ceilf((ch[i].hi[a] - org[a]) / sc), 0.0f);
+                if (__fmaf_rd(qh, sc, org[a]) < ch[i].hi[a]) qh += 1.0f;
+                ql = fmaxf(ql - 1.0f, 0.0f);
+                qh += 1.0f;
+                if (qh > 255.0f || ql > 255.0f) {
+                    ok = false;
+                    break;
+                }
+                qlo[a][i] = (uint8_t)ql;
+                qhi[a][i] = (uint8_t)qh;
+            }
+            if (ok || eb[a] >= 254u) break;
+            eb[a] += 1;
+        }
+    }
+    // slots: octant of the child's centre relative to the node centre (bit0 = +x, bit1 = +y, bit2 = +z)
+    int child_at[8];
+    for (int k = 0; k < 8; k++) child_at[k] = -1;
+    uint32_t used = 0;
+    for (int i = 0; i < cnt; i++) {
+        uint32_t want = 0;
+        for (int a = 0; a < 3; a++)
+            if (ch[i].lo[a] + ch[i].hi[a] > lo[a] + hi[a]) want |= 1u << a;
+        uint32_t sl = want;
+        if ((used >> sl) & 1u) {
+            int bd = 99;
+            for (uint32_t k = 0; k < 8; k++) {
+                const int d = __popc(k ^ want);
+                if (!((used >> k) & 1u) && d < bd) {
+                    bd = d;
+                    sl = k;
+                }
+            }
+        }
+        used |= 1u << sl;
+        child_at[sl] = i;
+    }
+    uint32_t imask = 0, n_int = 0, n_pr = 0;
+    for (int k = 0; k < 8; k++) {
+        const int i = child_at[k];
+        if (i < 0) continue;
+        if (ch[i].enc >= 0) {
+            imask |= 1u << k;
+            n_int += 1;
+        } else {
+            n_pr += (((uint32_t)ch[i].enc >> kLeafCountShift) & 7u) + 1u;
+        }
+    }
+    const uint32_t child_base = n_int ? atomicAdd(&info->n_wnodes, n_int) : 0u;
+    const uint32_t prim_base = n_pr ? atomicAdd(&info->n_wprims, n_pr) : 0u;
+    uint32_t meta[8], px[2] = {0, 0}, py[2] = {0, 0}, pz[2] = {0, 0}, hx[2] = {0, 0}, hy[2] = {0, 0}, hz[2] = {0, 0};
+    uint32_t rank = 0, off = 0;
+    for (int k = 0; k < 8; k++) {
+        const int i = child_at[k];
+        const int sh = 8 * (k & 3);
+        if (i < 0) {  // empty slot: inverted box, never hit
+            meta[k] = 0;
+            px[k >> 2] |= 255u << sh; py[k >> 2] |= 255u << sh; pz[k >> 2] |= 255u << sh;
+            continue;
+        }
+        px[k >> 2] |= (uint32_t)qlo[0][i] << sh; py[k >> 2] |= (uint32_t)qlo[1][i] << sh; pz[k >> 2] |= (uint32_t)qlo[2][i] << sh;
+        hx[k >> 2] |= (uint32_t)qhi[0][i] << sh; hy[k >> 2] |= (uint32_t)qhi[1][i] << sh; hz[k >> 2] |= (uint32_t)qhi[2][i] << sh;
+        if (ch[i].enc >= 0) {
+            meta[k] = 0x20u | (24u + (uint32_t)k);
+            wtask[child_base + rank] = (uint32_t)ch[i].enc;
+            rank += 1;
+        } else {
+            const uint32_t enc = (uint32_t)ch[i].enc;
+            const uint32_t c = ((enc >> kLeafCountShift) & 7u) + 1u, f = enc & kLeafFirstMask;
+            meta[k] = (((1u << c) - 1u) << 5) | off;
+            for (uint32_t t = 0; t < c; t++) {
+                wslot_geom[prim_base + off + t] = slot_geom[f + t];
+                wslot_prim[prim_base + off + t] = slot_prim[f + t];
+                wslot_mat[prim_base + off + t] = slot_mat[f + t];
+            }
+            off += c;
+        }
+    }
+    float4 *o = reinterpret_cast<float4 *>(wnodes + w);
+    o[0] = make_float4(org[0], org[1], org[2], __uint_as_float(eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24)));
+    o[1] = make_float4(__uint_as_float(child_base), __uint_as_float(prim_base),
+                       __uint_as_float(meta[0] | (meta[1] << 8) | (meta[2] << 16) | (meta[3] << 24)),
+                       __uint_as_float(meta[4] | (meta[5] << 8) | (meta[6] << 16) | (meta[7] << 24)));
+    o[2] = make_float4(__uint_as_float(px[0]), __uint_as_float(px[1]), __uint_as_float(py[0]), __uint_as_float(py[1]));
+    o[3] = make_float4(__uint_as_float(pz[0]), __uint_as_float(pz[1]), __uint_as_float(hx[0]), __uint_as_float(hx[1]));
+    o[4] = make_float4(__uint_as_float(hy[0]), __uint_as_float(hy[1]), __uint_as_float(hz[0]), __uint_as_float(hz[1]));
+}
+
+__global__ void __launch_bounds__(128)
+k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict__ wtask, WNode *__restrict__ wnodes,
+           const float4 *__restrict__ slot_geom, const uint32_t *__restrict__ slot_prim, const uint32_t *__restrict__ slot_mat,
+           float4 *__restrict__ wslot_geom, uint32_t *__restrict__ wslot_prim, uint32_t *__restrict__ wslot_mat) {
+    cg::grid_group grid = cg::this_grid();
+    const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    const uint32_t n = info->n_bvh;
+    // outlier primitives keep their positions behind the tree's primitives
+    for (uint32_t i = gtid; i < info->n_huge; i += gsize) {
+        wslot_geom[n + i] = slot_geom[n + i];
+        wslot_prim[n + i] = slot_prim[n + i];
+        wslot_mat[n + i] = slot_mat[n + i];
+    }
+    if (n == 0) return;  // uniform over the grid
+    if (gtid == 0) {
+        wtask[0] = 0;
+        info->n_wnodes = 1;
+        info->n_wprims = 0;
+    }
+    grid.sync();
+    uint32_t begin = 0, end = 1;
+    while (begin < end) {
+        for (uint32_t w = begin + gtid; w < end; w += gsize)
+            collapse_one(w, (int)wtask[w], nodes, info, wtask, wnodes, slot_geom, slot_prim, slot_mat, wslot_geom, wslot_prim, wslot_mat);
+        grid.sync();
+        begin = end;
+        end = *reinterpret_cast<volatile uint32_t *>(&info->n_wnodes);
+        grid.sync();
+    }
 }
 
 // ------------------------------------------------------------------ host driver
@@ -562,6 +781,12 @@ int build_accel(Scene *s, cudaStream_t st) {
     RT_CUDA(ctx, s->slot_prim.reserve(n1, &s->bytes));
     RT_CUDA(ctx, s->slot_mat.reserve(n1, &s->bytes));
     RT_CUDA(ctx, s->info.reserve(1, &s->bytes));
+    if (s->wide) {
+        RT_CUDA(ctx, s->wnodes.reserve(n1, &s->bytes));
+        RT_CUDA(ctx, s->wslot_geom.reserve(n1, &s->bytes));
+        RT_CUDA(ctx, s->wslot_prim.reserve(n1, &s->bytes));
+        RT_CUDA(ctx, s->wslot_mat.reserve(n1, &s->bytes));
+    }
 
     if (!s->ev[0]) {
         for (int k = 0; k < 4; k++) RT_CUDA(ctx, cudaEventCreate(&s->ev[k]));
@@ -594,12 +819,35 @@ int build_accel(Scene *s, cudaStream_t st) {
         }
         // 4 passes: result back in buffer 0
         k_gather<<<gb, 256, 0, st>>>(s->vals[0].p, s->w_geom.p, s->w_mat.p, n, s->slot_geom.p, s->slot_prim.p, s->slot_mat.p);
-        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)s->leaf_max);
+        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? std::min(s->leaf_max, kWideLeafMax) : s->leaf_max));
         k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
         s->launches += 3;
     }
     k_small_tree<<<1, 32, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p);
     s->launches += 1;
+    if (n) {
+        k_huge_boxes<<<1, 32, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p);
+        s->launches += 1;
+    }
+    if (s->wide) {
+        if (!ctx->collapse_blocks) {
+            int per_sm = 0;
+            RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_collapse, 128, 0));
+            if (per_sm < 1) return set_error(ctx, RT_ERR_CUDA, "k_collapse cannot be resident");
+            ctx->collapse_blocks = per_sm * ctx->sm_count;
+        }
+        const Node *a_nodes = s->nodes.p;
+        BuildInfo *a_info = s->info.p;
+        uint32_t *a_task = s->parent_leaf.p;  // free after the refit
+        WNode *a_wn = s->wnodes.p;
+        const float4 *a_sg = s->slot_geom.p;
+        const uint32_t *a_sp = s->slot_prim.p, *a_sm = s->slot_mat.p;
+        float4 *a_wg = s->wslot_geom.p;
+        uint32_t *a_wp = s->wslot_prim.p, *a_wm = s->wslot_mat.p;
+        void *args[] = {&a_nodes, &a_info, &a_task, &a_wn, &a_sg, &a_sp, &a_sm, &a_wg, &a_wp, &a_wm};
+        RT_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)k_collapse, dim3((unsigned)ctx->collapse_blocks), dim3(128), args, 0, st));
+        s->launches += 1;
+    }
     RT_CUDA(ctx, cudaEventRecord(s->ev[1], st));
     RT_CUDA(ctx, cudaGetLastError());
     s->have_build_ev = true;
@@ -611,9 +859,10 @@ int build_accel(Scene *s, cudaStream_t st) {
 SceneDev scene_dev(const Scene *s) {
     SceneDev d;
     d.nodes = s->nodes.p;
-    d.slot_geom = s->slot_geom.p;
-    d.slot_prim = s->slot_prim.p;
-    d.slot_mat = s->slot_mat.p;
+    d.wnodes = s->wnodes.p;
+    d.slot_geom = s->wide ? s->wslot_geom.p : s->slot_geom.p;
+    d.slot_prim = s->wide ? s->wslot_prim.p : s->slot_prim.p;
+    d.slot_mat = s->wide ? s->wslot_mat.p : s->slot_mat.p;
     d.tri_v12 = s->tri_v12.p;
     d.tri_nrm = s->tri_nrm.p;
     d.roughs = s->d_roughs.p;

@@ -325,4 +325,223 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
     }
 }
 
+// ------------------------------------------------------------------ 8-wide compressed BVH traversal
+// Same two-phase warp scheme as extend_warp, over WNode (rt_internal.h).  A lane keeps
+//   (gbase, gmask): current node group = child_base + [31:24] pending internal-child hits placed at
+//                   their traversal priority (slot ^ octinv, nearer octant = higher bit), [7:0] imask;
+//   (pbase, pmask), (pbase2, pmask2): up to two postponed primitive groups (bit k = prim_base + k).
+// The stack holds node groups only (8 bytes each).  Children are visited in octant order, which is
+// a heuristic only: every hit child is eventually visited, so the closest hit equals brute force.
+#define RT_WSTACK 64
+
+// byte j of w as the float 2^23 + q (exact): the 2^23 is folded into the FMA addend of the slab test.
+// That addend is rounded once, which can move a child plane by up to half a quantisation step; the
+// build widens every quantised box by one step per side to stay conservative (collapse_one).
+template <int J>
+__device__ __forceinline__ float qfloat(uint32_t w, uint32_t magic) {
+    // prmt with the selector as the immediate and 0x4B000000 in a register (the compiler otherwise
+    // inlines the constant and spends a register move per selector)
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x7650 + J));
+    return __uint_as_float(r);
+}
+// per byte: 0xFF if its sign bit is set, else 0x00 (prmt selector msb = replicate the sign of the byte;
+// __byte_perm() only honours 3 selector bits, so this is spelled in PTX)
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(r) : "r"(x));
+    return r;
+}
+
+#define QF(w, j) ((j) == 0 ? qfloat<0>(w, magic) : (j) == 1 ? qfloat<1>(w, magic) : (j) == 2 ? qfloat<2>(w, magic) : qfloat<3>(w, magic))
+
+// `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
+__device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
+                                                 float4 *__restrict__ hits, int t1, int t2, int fetch_min, uint32_t magic) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    const float4 *wn = reinterpret_cast<const float4 *>(sc.wnodes);
+    const BuildInfo *info = sc.info;
+    const uint32_t n_huge = info->n_huge;
+    const bool have_tree = info->n_bvh != 0;
+
+    uint2 stack[RT_WSTACK];
+    int sp = 0;
+    uint32_t gbase = 0, gmask = 0, pbase = 0, pmask = 0, pbase2 = 0, pmask2 = 0;
+    bool huge_done = true;
+    uint32_t idx = 0, skip_slot = kNoSlot, octinv = 0;
+    Ray r;
+    r.o = r.d = f3(0, 0, 0);
+    r.tmin = RT_ZERO;
+    r.tmax = RT_INF;
+    Hit best;
+    best.t = 0.0f;
+    best.slot = kNoSlot;
+    best.u = best.v = 0.0f;
+    float a = 1.0f, inv_a = 1.0f, ix = 0, iy = 0, iz = 0, ox = 0, oy = 0, oz = 0;
+    bool alive = false, exhausted = false;
+
+    for (;;) {
+        // ---- dynamic fetch
+        const uint32_t dead = __ballot_sync(FULL, !alive);
+        if (dead && !exhausted && (dead == FULL || __popc(dead) >= fetch_min)) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(fetch_ctr, (uint32_t)__popc(dead));
+            base = __shfl_sync(FULL, base, 0);
+            if (base + __popc(dead) >= n) exhausted = true;
+            const uint32_t i = base + __popc(dead & lt);
+            if (!alive && i < n) {
+                const float4 o4 = in.o[i], d4 = in.d[i];
+                idx = i;
+                r.o = f3(o4.x, o4.y, o4.z);
+                r.d = f3(d4.x, d4.y, d4.z);
+                if (in.skip) {
+                    r.tmin = o4.w;
+                    r.tmax = d4.w;
+                    skip_slot = in.skip[i];
+                } else {
+                    r.tmin = RT_ZERO;  // Shader.cu:231-233, 264-267
+                    r.tmax = RT_INF;
+                    skip_slot = __float_as_uint(d4.w);
+                }
+                best.t = r.tmax;
+                best.slot = kNoSlot;
+                best.u = best.v = 0.0f;
+                a = dot(r.d, r.d);
+                inv_a = 1.0f / a;
+                const float ex = fabsf(r.d.x) < 1e-30f ? copysignf(1e-30f, r.d.x) : r.d.x;
+                const float ey = fabsf(r.d.y) < 1e-30f ? copysignf(1e-30f, r.d.y) : r.d.y;
+                const float ez = fabsf(r.d.z) < 1e-30f ? copysignf(1e-30f, r.d.z) : r.d.z;
+                ix = 1.0f / ex; iy = 1.0f / ey; iz = 1.0f / ez;
+                ox = -r.o.x * ix; oy = -r.o.y * iy; oz = -r.o.z * iz;
+                octinv = (ix >= 0.0f ? 1u : 0u) | (iy >= 0.0f ? 2u : 0u) | (iz >= 0.0f ? 4u : 0u);
+                octinv *= 0x01010101u;  // replicated per byte for the 4-children-at-a-time mask maths
+                huge_done = n_huge == 0;
+                sp = 0;
+                pmask = pmask2 = 0;
+                gbase = 0;
+                gmask = have_tree ? 0x80000000u : 0u;  // root: slot 7^octinv of an imask-0 group -> index 0
+                alive = true;
+            }
+        }
+        if (!__any_sync(FULL, alive)) break;
+
+        // ---- phase 1: wide nodes
+        bool first = true;
+        for (;;) {
+            const bool want = alive && pmask2 == 0 && ((gmask >> 24) != 0 || sp > 0);
+            const uint32_t mw = __ballot_sync(FULL, want);
+            if (!mw) break;
+            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && pmask != 0)) break;
+            first = false;
+            if (want) {
+                if ((gmask >> 24) == 0) {
+                    const uint2 e = stack[--sp];
+                    gbase = e.x;
+                    gmask = e.y;
+                }
+                const uint32_t bit = 31u - (uint32_t)__clz(gmask);
+                gmask &= ~(1u << bit);
+                const uint32_t slot = (bit - 24u) ^ (octinv & 7u);
+                const uint32_t child = gbase + __popc(gmask & ((1u << slot) - 1u));
+                if (gmask >> 24) stack[sp++] = make_uint2(gbase, gmask);
+
+                const float4 *q = wn + 5 * (size_t)child;
+                const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
+                const uint32_t eim = __float_as_uint(w0.w);
+                const float sx = __uint_as_float((eim & 0xFFu) << 23) * ix;
+                const float sy = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * iy;
+                const float sz = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * iz;
+                // t = (2^23 + q) * s + (b - 2^23 * s), b = (origin - o) / d
+                const float bx = __fmaf_rn(-8388608.0f, sx, __fmaf_rn(w0.x, ix, ox));
+                const float by = __fmaf_rn(-8388608.0f, sy, __fmaf_rn(w0.y, iy, oy));
+                const float bz = __fmaf_rn(-8388608.0f, sz, __fmaf_rn(w0.z, iz, oz));
+                const bool px = ix >= 0.0f, py = iy >= 0.0f, pz = iz >= 0.0f;
+                uint32_t hitmask = 0;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const uint32_t lox = __float_as_uint(h ? w2.y : w2.x), loy = __float_as_uint(h ? w2.w : w2.z);
+                    const uint32_t loz = __float_as_uint(h ? w3.y : w3.x), hix = __float_as_uint(h ? w3.w : w3.z);
+                    const uint32_t hiy = __float_as_uint(h ? w4.y : w4.x), hiz = __float_as_uint(h ? w4.w : w4.z);
+                    const uint32_t nx = px ? lox : hix, fx = px ? hix : lox;
+                    const uint32_t ny = py ? loy : hiy, fy = py ? hiy : loy;
+                    const uint32_t nz = pz ? loz : hiz, fz = pz ? hiz : loz;
+                    // per byte: which bit of the hit mask a child owns and how many bits (leaf = unary count)
+                    const uint32_t meta4 = __float_as_uint(h ? w1.w : w1.z);
+                    const uint32_t inner4 = sign_extend_s8x4(((meta4 & (meta4 << 1)) & 0x10101010u) << 3);
+                    const uint32_t bit4 = (meta4 ^ (octinv & inner4 & 0x07070707u)) & 0x1F1F1F1Fu;
+                    const uint32_t cnt4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float tnx = __fmaf_rn(QF(nx, j), sx, bx), tfx = __fmaf_rn(QF(fx, j), sx, bx);
+                        const float tny = __fmaf_rn(QF(ny, j), sy, by), tfy = __fmaf_rn(QF(fy, j), sy, by);
+                        const float tnz = __fmaf_rn(QF(nz, j), sz, bz), tfz = __fmaf_rn(QF(fz, j), sz, bz);
+                        const float tlo = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));
+                        const float thi = fminf(fminf(tfx, tfy), fminf(tfz, best.t));
+                        if (tlo <= thi * 1.000002f)  // empty slots have count bits 0 and an inverted box
+                            hitmask |= ((cnt4 >> (8 * j)) & 0xFFu) << ((bit4 >> (8 * j)) & 0xFFu);
+                    }
+                }
+                gbase = __float_as_uint(w1.x);
+                gmask = (hitmask & 0xFF000000u) | (eim >> 24);
+                const uint32_t pm = hitmask & 0x00FFFFFFu;
+                if (pm) {
+                    if (pmask == 0) {
+                        pbase = __float_as_uint(w1.y);
+                        pmask = pm;
+                    } else {
+                        pbase2 = __float_as_uint(w1.y);
+                        pmask2 = pm;
+                    }
+                }
+            }
+        }
+
+        // ---- phase 2: postponed primitives, one per iteration
+        first = true;
+        for (;;) {
+            const bool hl = alive && pmask != 0;
+            const uint32_t ml = __ballot_sync(FULL, hl);
+            if (!ml) break;
+            if (!first && __popc(ml) < t2 &&
+                __any_sync(FULL, alive && pmask2 == 0 && ((gmask >> 24) != 0 || sp > 0)))
+                break;
+            first = false;
+            if (hl) {
+                const uint32_t b = (uint32_t)__ffs(pmask) - 1u;
+                pmask &= pmask - 1u;
+                test_slot(sc, r, a, inv_a, pbase + b, skip_slot, best);
+                if (pmask == 0 && pmask2 != 0) {
+                    pbase = pbase2;
+                    pmask = pmask2;
+                    pmask2 = 0;
+                }
+            }
+        }
+
+        // ---- rays whose tree walk is over: outlier primitives (BuildInfo.huge_*), culled by their boxes
+        //      against the closest hit found so far, go through phase 2 as one last primitive group
+        if (alive && !huge_done && (gmask >> 24) == 0 && sp == 0 && pmask == 0) {
+            huge_done = true;
+            uint32_t m = 0;
+            for (uint32_t k = 0; k < n_huge; k++) {
+                const float x0 = __fmaf_rn(info->huge_lo[k][0], ix, ox), x1 = __fmaf_rn(info->huge_hi[k][0], ix, ox);
+                const float y0 = __fmaf_rn(info->huge_lo[k][1], iy, oy), y1 = __fmaf_rn(info->huge_hi[k][1], iy, oy);
+                const float z0 = __fmaf_rn(info->huge_lo[k][2], iz, oz), z1 = __fmaf_rn(info->huge_hi[k][2], iz, oz);
+                const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
+                const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best.t));
+                if (tlo <= thi * 1.000002f) m |= 1u << k;
+            }
+            pbase = info->huge_slot[0];
+            pmask = m;
+        }
+        // ---- retire finished rays
+        if (alive && huge_done && (gmask >> 24) == 0 && sp == 0 && pmask == 0) {
+            hits[idx] = make_float4(best.slot == kNoSlot ? RT_INF : best.t, __uint_as_float(best.slot), best.u, best.v);
+            alive = false;
+        }
+    }
+}
+
 }  // namespace rtb

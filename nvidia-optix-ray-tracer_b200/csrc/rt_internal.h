@@ -43,6 +43,23 @@ struct alignas(16) Node {
     float4 n0, n1, n2, n3;
 };
 
+// 80-byte 8-wide node with 8-bit quantised child boxes (layout after Ylitie, Karras, Laine 2017,
+// "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"), collapsed from the
+// binary LBVH every frame.  Five 128-bit words:
+//   w0 = origin.x origin.y origin.z  bits(ex | ey<<8 | ez<<16 | imask<<24)   (scale_a = 2^(e_a-127))
+//   w1 = bits(child_base) bits(prim_base) bits(meta[0..3]) bits(meta[4..7])
+//   w2 = qlo_x[0..3] qlo_x[4..7] qlo_y[0..3] qlo_y[4..7]
+//   w3 = qlo_z[0..3] qlo_z[4..7] qhi_x[0..3] qhi_x[4..7]
+//   w4 = qhi_y[0..3] qhi_y[4..7] qhi_z[0..3] qhi_z[4..7]
+// child box a-axis = origin_a + q * scale_a.  meta[i]: 0 = empty slot; internal child: 0x20 | (24+i);
+// leaf: (unary(count 1..3) << 5) | offset of its first primitive from prim_base (0..23).
+// Internal children are stored contiguously from child_base in slot order; the leaf primitives of a
+// node are contiguous from prim_base in slot order (primitives are re-packed per wide node).
+struct alignas(16) WNode {
+    float4 w0, w1, w2, w3, w4;
+};
+constexpr uint32_t kWideLeafMax = 3;
+
 constexpr uint32_t kLeafFlag = 0x80000000u;
 constexpr uint32_t kLeafFirstMask = 0x07FFFFFFu;
 constexpr int kLeafCountShift = 27;
@@ -60,10 +77,16 @@ struct BuildInfo {
     int32_t huge_bucket;  // prims whose extent bucket is > this are "huge"
     float scene_lo[3], scene_hi[3];  // root bounds after refit
     uint32_t huge_slot[kMaxHuge];    // slots (sorted order positions) of huge prims
+    float huge_lo[kMaxHuge][3], huge_hi[kMaxHuge][3];  // padded boxes of the huge prims
+    uint32_t n_wnodes;               // wide nodes allocated by the collapse (also its task-queue tail)
+    uint32_t n_wprims;               // primitives re-packed by the collapse
+    uint32_t level_end;              // collapse: end of the current level in the task queue
+    uint32_t pad_;
 };
 
 struct SceneDev {  // everything a traversal needs, passed by value to kernels
-    const Node *nodes;
+    const Node *nodes;          // binary LBVH (traversed when option "wide" is 0)
+    const WNode *wnodes;        // 8-wide compressed BVH
     const float4 *slot_geom;    // sphere: c.xyz r   | triangle: v0.xyz, bits(0x80000000|tri index)
     const uint32_t *slot_prim;  // global primitive id per slot
     const uint32_t *slot_mat;   // (mat_type<<31)|index per slot
@@ -105,6 +128,7 @@ struct DevBuf {  // grow-only device buffer
 struct Context {
     int device = 0;
     int sm_count = 148;
+    int collapse_blocks = 0;  // co-resident grid of the cooperative collapse kernel
     std::mutex mu;
     std::string last_error;
 };
@@ -147,6 +171,10 @@ struct Scene {
     DevBuf<uint32_t> parent_int, parent_leaf, visit;
     DevBuf<float4> slot_geom;
     DevBuf<uint32_t> slot_prim, slot_mat;
+    DevBuf<WNode> wnodes;         // wide BVH + primitives re-packed per wide node
+    DevBuf<float4> wslot_geom;
+    DevBuf<uint32_t> wslot_prim, wslot_mat;
+    bool wide = true;             // traverse the 8-wide BVH (default) or the binary LBVH
     DevBuf<BuildInfo> info;
 
     // render
@@ -163,7 +191,7 @@ struct Scene {
     DevBuf<float4> result;        // per path
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
     DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
-    uint32_t t1 = 12, t2 = 12, fetch_min = 12;  // traversal thresholds (see extend_warp)
+    uint32_t t1 = 8, t2 = 8, fetch_min = 4;  // traversal thresholds (see extend_warp)
     uint32_t extend_blocks_per_sm = 8;
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;

@@ -145,6 +145,14 @@ k_extend(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t 
     extend_warp(sc, in, n, fetch_ctr, hits, t1, t2, fetch_min);
 }
 
+template <int kMinBlocks>
+__global__ void __launch_bounds__(128, kMinBlocks)
+k_extend_wide(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t n_fixed, uint32_t *fetch_ctr,
+              float4 *__restrict__ hits, int t1, int t2, int fetch_min, uint32_t magic) {
+    const uint32_t n = n_ptr ? *n_ptr : n_fixed;
+    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, fetch_min, magic);
+}
+
 // ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
 // One ray per pixel, written in pixel order into the path-queue layout (path id = pixel, no skip).
 __global__ void __launch_bounds__(128)
@@ -392,7 +400,16 @@ static int launch_extend(Scene *s, const SceneDev &sd, const ExtendIn &in, const
     uint32_t grid = (uint32_t)ctx->sm_count * s->extend_blocks_per_sm;
     if (!n_ptr) grid = std::min(grid, std::max(1u, div_up(n_fixed, 128u)));
     RT_CUDA(ctx, prof_mark(s, st));
-    k_extend<<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min);
+    if (s->wide) {
+        if (s->extend_blocks_per_sm >= 8)
+            k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+        else if (s->extend_blocks_per_sm >= 6)
+            k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+        else
+            k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+    }
+    else
+        k_extend<<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min);
     RT_CUDA(ctx, prof_mark(s, st));
     s->launches += 1;
     return RT_OK;
@@ -537,7 +554,7 @@ int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, floa
     RT_CUDA(ctx, s->u_skip.reserve(n + 1, &s->bytes));
     // vals[1] is free after the build: reuse it as the gid -> slot map
     if (skip && s->n_prims) {
-        k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(s->slot_prim.p, s->n_prims, s->vals[1].p);
+        k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(scene_dev(s).slot_prim, s->n_prims, s->vals[1].p);
         s->launches += 1;
     }
     k_pack_rays<<<div_up((uint32_t)n, 128), 128, 0, st>>>(rays, skip, s->vals[1].p, (uint32_t)n, s->q_o[0].p, s->q_d[0].p, s->u_skip.p);

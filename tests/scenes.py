@@ -110,7 +110,7 @@ def flatten_world(desc: SceneDesc):
 class GpuScene:
     """Uploads a SceneDesc through the C ABI (device memory held by torch tensors)."""
 
-    def __init__(self, pkg, desc: SceneDesc, ctx=None, device="cuda:0"):
+    def __init__(self, pkg, desc: SceneDesc, ctx=None, device="cuda:0", options=None):
         import torch
         self.torch = torch
         self.pkg = pkg
@@ -134,6 +134,8 @@ class GpuScene:
                 self.scene.add_triangles(a.data_ptr() if n else None, b.data_ptr() if n else None, n)
         for inst in desc.instances:
             self.scene.add_instance(inst["group"], list(inst["m"]), inst["mat_type"], inst["mat_index"], inst["mat_stride"])
+        for k, v in (options or {}).items():
+            self.scene.set_option(k, v)
         self.scene.build()
 
     def render(self, cam, width, height, spp, max_depth, seed, background=(0.7, 0.8, 0.9), sample_offset=0, flags=0,

@@ -74,7 +74,7 @@ def check_tree(st, nodes, prim, keys, world):
 def test_tree_invariants(pkg, synth, n, ntri, ground):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
     world = scenes.flatten_world(d)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options={"wide": 0})
     st, nodes, geom, prim, keys = download(gs, len(world["kind_index"]))
     assert int(st.n_prims) == len(world["kind_index"])
     assert int(st.n_huge) == (1 if ground else 0)
@@ -102,7 +102,7 @@ def test_duplicate_morton_keys(pkg, synth):
     g = d.add_spheres(c, r)
     d.add_instance(g, None, 0, 0, 0)
     world = scenes.flatten_world(d)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options={"wide": 0})
     st, nodes, geom, prim, keys = download(gs, 300)
     assert len(np.unique(keys)) < 250
     check_tree(st, nodes, prim, keys, world)
@@ -115,7 +115,7 @@ def test_rebuild_is_deterministic_and_tracks_motion(pkg, synth):
     d = scenes.SceneDesc(scenes.CONFIG_ROUGHS, scenes.CONFIG_METALS)
     g = d.add_spheres(centers, radii)
     d.add_instance(g, None, 0, 0, 0)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options={"wide": 0})
     st1, n1, g1, p1, k1 = download(gs, 20000)
     gs.scene.build()
     st2, n2, g2, p2, k2 = download(gs, 20000)
@@ -129,6 +129,89 @@ def test_rebuild_is_deterministic_and_tracks_motion(pkg, synth):
     check_tree(st3, n3, p3, k3, scenes.flatten_world(d))
     assert abs(st3.scene_lo[2] - (st1.scene_lo[2] - 0.05)) < 1e-4
     assert st3.build_ms > 0
+    gs.close()
+
+
+def check_wide_tree(gs, world):
+    """8-wide compressed BVH: every primitive referenced exactly once, every child's decoded box
+    contains its primitives' boxes / its children's decoded boxes, internal children contiguous."""
+    n = len(world["kind_index"])
+    st = gs.scene.stats()
+    n_bvh = int(st.n_bvh_prims)
+    nn = gs.scene.download_wide()
+    assert nn == int(st.n_nodes)
+    wn = np.zeros((max(nn, 1), 20), np.float32)
+    geom = np.zeros((max(n, 1), 4), np.float32)
+    prim = np.zeros(max(n, 1), np.uint32)
+    gs.scene.download_wide(wn.ctypes.data, geom.ctypes.data, prim.ctypes.data)
+    prim = prim[:n]
+    assert sorted(prim.tolist()) == list(range(n)), "re-packed slot_prim must be a permutation of the global ids"
+    if n_bvh == 0:
+        return
+    wu = wn.view(np.uint32)
+    seen = np.zeros(n, np.int32)
+    node_seen = np.zeros(nn, np.int32)
+    stack = [(0, [])]
+    while stack:
+        w, anc = stack.pop()
+        node_seen[w] += 1
+        org = wn[w, 0:3].astype(np.float64)
+        eim = int(wu[w, 3])
+        scale = np.array([2.0 ** (((eim >> (8 * a)) & 0xFF) - 127) for a in range(3)])
+        imask = eim >> 24
+        child_base, prim_base = int(wu[w, 4]), int(wu[w, 5])
+        meta = wu[w, 6:8].copy().view(np.uint8)
+        q = wu[w, 8:20].copy().view(np.uint8).reshape(6, 8)  # qlo_x qlo_y qlo_z qhi_x qhi_y qhi_z
+        rank = 0
+        for k in range(8):
+            m = int(meta[k])
+            if m == 0:
+                assert not (imask >> k) & 1
+                continue
+            lo = org + q[0:3, k] * scale
+            hi = org + q[3:6, k] * scale
+            assert np.all(lo <= hi)
+            if (m & 0x18) == 0x18:
+                assert (m & 7) == k and (m >> 5) == 1 and (imask >> k) & 1
+                stack.append((child_base + rank, anc + [(lo, hi)]))
+                rank += 1
+            else:
+                assert not (imask >> k) & 1
+                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                off = m & 31
+                for s in range(prim_base + off, prim_base + off + cnt):
+                    assert s < n_bvh
+                    seen[s] += 1
+                    plo, phi = slot_box(world, int(prim[s]))
+                    # quantised boxes are each conservative for the primitives below them (a child's own
+                    # grid may stick out of its parent's slot box by a quantum, which is harmless)
+                    for blo, bhi in anc + [(lo, hi)]:
+                        assert np.all(plo >= blo) and np.all(phi <= bhi), "a box on the path does not contain the primitive"
+    assert np.all(seen[:n_bvh] == 1), "every BVH primitive must be in exactly one wide leaf"
+    assert np.all(node_seen == 1), "every wide node must be reachable exactly once"
+
+
+@pytest.mark.parametrize("n,ntri,ground", [(1, 0, False), (2, 0, False), (5, 3, False), (64, 16, True), (1000, 200, True), (30000, 0, False)])
+def test_wide_tree_invariants(pkg, synth, n, ntri, ground):
+    d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
+    world = scenes.flatten_world(d)
+    gs = scenes.GpuScene(pkg, d)
+    check_wide_tree(gs, world)
+    gs.scene.build()  # rebuild over the same buffers: same invariants
+    check_wide_tree(gs, world)
+    gs.close()
+
+
+def test_wide_tree_duplicate_keys(pkg):
+    c = np.zeros((300, 3), np.float32)
+    c[:200] = [0.1, 0.1, 0.1]
+    c[200:] = np.random.default_rng(0).uniform(-0.4, 0.4, (100, 3))
+    r = np.linspace(0.01, 0.03, 300).astype(np.float32)
+    d = scenes.SceneDesc(scenes.CONFIG_ROUGHS, scenes.CONFIG_METALS)
+    g = d.add_spheres(c, r)
+    d.add_instance(g, None, 0, 0, 0)
+    gs = scenes.GpuScene(pkg, d)
+    check_wide_tree(gs, scenes.flatten_world(d))
     gs.close()
 
 

@@ -78,11 +78,12 @@ def test_random_scene_golden_fixture(pkg, synth):
     (2000, 300, 4, 8, (200, 120)),   # rough + metal + fuzz, triangles under a rotated instance
     (20000, 0, 5, 5, (256, 144)),    # spp not a multiple of the sample batch
 ])
-def test_image_parity_vs_oracle(pkg, synth, oracle, n, ntri, spp, depth, res):
+@pytest.mark.parametrize("wide", [1, 0])
+def test_image_parity_vs_oracle(pkg, synth, oracle, n, ntri, spp, depth, res, wide):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n + 1, metal_every=7 if n > 10 else 0, fuzz=0.25,
                             with_walls=n != 0, with_ground=n >= 50)
     cam = pkg.camera_configure([2.2, 0.2, 0.3], [0, 0, 0], [0, 0, 1], False)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options={"wide": wide})
     g = gs.render(cam, res[0], res[1], spp, depth, 7 + n)
     o = oracle.render(scenes.flatten_world(d), cam, res[0], res[1], spp, depth, 7 + n, accel=1 if n > 500 else 0)
     assert_images_equal(g, o, spp)
@@ -90,7 +91,9 @@ def test_image_parity_vs_oracle(pkg, synth, oracle, n, ntri, spp, depth, res):
     gs.close()
 
 
-def test_trace_rays_equals_brute_force(pkg, synth, oracle):
+@pytest.mark.parametrize("opts", [{"wide": 1}, {"wide": 0}, {"wide": 1, "t1": 0, "t2": 0, "fetch_min": 32},
+                                  {"wide": 1, "t1": 33, "t2": 33, "fetch_min": 1}, {"wide": 0, "t1": 33, "t2": 0, "fetch_min": 5}])
+def test_trace_rays_equals_brute_force(pkg, synth, oracle, opts):
     """BVH traversal == brute force over all primitives on random rays (incl. axis-parallel ones and
     self-exclusion), the property that makes primary ids independent of the tree."""
     d = scenes.random_scene(pkg, synth, 30000, n_tris=3000, seed=21, with_ground=True)
@@ -104,7 +107,7 @@ def test_trace_rays_equals_brute_force(pkg, synth, oracle):
     dd[400:600] *= 1e-3   # un-normalised directions: t is in units of |d|
     dd[600:800] *= 1e3
     rays = np.concatenate([o, np.full((n, 1), 1e-6, np.float32), dd, np.full((n, 1), 1e16, np.float32)], 1)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options=opts)
     t0, i0 = oracle.trace(w, rays, accel=0)
     t1, i1 = gs.trace(rays)
     assert np.array_equal(i0, i1)
