@@ -191,9 +191,8 @@ def run_ours(a):
     import torch.distributed as dist
     pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
     synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
-    world_size = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    mg = importlib.import_module("nvidia-optix-ray-tracer_b200.multigpu")
+    rank, local, world_size = mg.env_world()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -201,8 +200,7 @@ def run_ours(a):
     if world_size > 1:
         dist.init_process_group("nccl", device_id=dev)
     assert world_size == a.gpus or world_size == 1 and a.gpus == 1, f"launch with torchrun --nproc-per-node {a.gpus}"
-    assert a.spp % world_size == 0, "spp must divide evenly over the ranks"
-    spp_rank = a.spp // world_size
+    spp_rank = mg.spp_partition(a.spp, world_size, rank)[1]
 
     host = build_scene_host(a, pkg, synth)
     cam = pkg.camera_configure(**synth.c4_camera())
@@ -241,10 +239,10 @@ def run_ours(a):
             d_centers.copy_(h_centers, non_blocking=True)
             d_radii.copy_(h_radii, non_blocking=True)
         sc.build(stream)
-        sc.render(cam, a.width, a.height, spp_rank, a.depth, a.seed + step, (0.7, 0.8, 0.9), rank * spp_rank, 0,
-                  accum.data_ptr(), None, None, None, stream)
-        if world_size > 1:
-            dist.reduce(accum, 0, op=dist.ReduceOp.SUM)
+        # per-pixel XORWOW streams continue from frame to frame as in the reference (states are initialised
+        # once, src/Global/RendererTime.cu:395): frame `step` owns samples [step*spp, (step+1)*spp)
+        mg.render_spp_split(sc, cam, a.width, a.height, a.spp, a.depth, a.seed, accum, frame=step, stream=stream,
+                            rank=rank, world=world_size)
         if rank == 0:
             ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
             if e2e:

@@ -743,7 +743,7 @@ int build_accel(Scene *s, cudaStream_t st) {
         }
     }
     base[s->insts.size()] = (uint32_t)np;
-    if (np >= (1ull << 27) && s->leaf_max > 1)
+    if (np >= (1ull << 27))
         return set_error(ctx, RT_ERR_UNSUPPORTED, "more than 2^27 primitives (%llu)", (unsigned long long)np);
     if (np >= 0x7FFFFFFFull) return set_error(ctx, RT_ERR_UNSUPPORTED, "too many primitives");
     const uint32_t n = (uint32_t)np;
@@ -819,7 +819,7 @@ int build_accel(Scene *s, cudaStream_t st) {
         }
         // 4 passes: result back in buffer 0
         k_gather<<<gb, 256, 0, st>>>(s->vals[0].p, s->w_geom.p, s->w_mat.p, n, s->slot_geom.p, s->slot_prim.p, s->slot_mat.p);
-        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? std::min(s->leaf_max, kWideLeafMax) : s->leaf_max));
+        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? (s->leaf_max ? std::min(s->leaf_max, kWideLeafMax) : 1u) : (s->leaf_max ? s->leaf_max : 4u)));
         k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
         s->launches += 3;
     }

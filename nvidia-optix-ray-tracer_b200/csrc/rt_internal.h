@@ -147,7 +147,7 @@ struct Scene {
     bool topo_dirty = true;   // groups/instances changed -> re-upload tables
     bool built = false;
     uint32_t n_prims = 0, n_tris = 0;
-    uint32_t leaf_max = 4;
+    uint32_t leaf_max = 0;        // 0 = auto: 1 primitive per leaf under the 8-wide tree, 4 under the binary LBVH
     uint32_t batch_spp = 4;
     size_t bytes = 0;
     uint64_t launches = 0;

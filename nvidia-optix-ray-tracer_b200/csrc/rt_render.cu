@@ -54,18 +54,51 @@ __device__ __forceinline__ Ray primary_ray(const CamDev &cam, uint32_t x, uint32
 // ------------------------------------------------------------------ RNG state init (HostFunctions.cu:122-127)
 // seed fixed by the caller (the reference xors clock64() in: quirk 7), subsequence = pixel,
 // offset = sample_offset * 64; bounds-checked and unpadded (quirk 8).
+// cuRAND's sequence skip costs ~20 GF(2) matrix-vector products (160x160 bits each) per state.  The
+// states of consecutive pixels differ by ONE application of the sequence-skip matrix
+// S = precalc_xorwow_matrix[0] (state(p+1) = S * state(p): all skips are powers of the same one-step
+// matrix and commute), so each thread pays curand_init once, for the first pixel of a run of
+// kRngRun, and then walks the run with one matrix-vector product per pixel.  GF(2) arithmetic is
+// exact: the states are bit-identical to curand_init(seed, p, offset) (checked against the oracle,
+// which calls the real thing per pixel).  d (the Weyl counter) depends on seed and offset only.
+constexpr uint32_t kRngRun = 64;
 __global__ void __launch_bounds__(128)
 k_rng_init(uint32_t *__restrict__ rng, uint32_t npix, unsigned long long seed, unsigned long long offset) {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
+    __shared__ uint4 s_row[160][2];  // row i of S padded to 8 words: one 128-bit + one 32-bit shared load
+    for (uint32_t i = threadIdx.x; i < 160; i += blockDim.x) {
+        const unsigned int *m = &precalc_xorwow_matrix[0][5 * i];
+        s_row[i][0] = make_uint4(m[0], m[1], m[2], m[3]);
+        s_row[i][1] = make_uint4(m[4], 0u, 0u, 0u);
+    }
+    __syncthreads();
+    const uint32_t p0 = (blockIdx.x * blockDim.x + threadIdx.x) * kRngRun;
+    if (p0 >= npix) return;
     curandStateXORWOW st;
-    curand_init(seed, (unsigned long long)p, offset, &st);
-    rng[0 * (size_t)npix + p] = st.d;
-    rng[1 * (size_t)npix + p] = st.v[0];
-    rng[2 * (size_t)npix + p] = st.v[1];
-    rng[3 * (size_t)npix + p] = st.v[2];
-    rng[4 * (size_t)npix + p] = st.v[3];
-    rng[5 * (size_t)npix + p] = st.v[4];
+    curand_init(seed, (unsigned long long)p0, offset, &st);
+    uint32_t v[5] = {st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
+    const uint32_t end = min(p0 + kRngRun, npix);
+    for (uint32_t p = p0; p < end; p++) {
+        rng[0 * (size_t)npix + p] = st.d;
+        rng[1 * (size_t)npix + p] = v[0];
+        rng[2 * (size_t)npix + p] = v[1];
+        rng[3 * (size_t)npix + p] = v[2];
+        rng[4 * (size_t)npix + p] = v[3];
+        rng[5 * (size_t)npix + p] = v[4];
+        if (p + 1 == end) break;
+        uint32_t y0 = 0, y1 = 0, y2 = 0, y3 = 0, y4 = 0;
+#pragma unroll
+        for (int w = 0; w < 5; w++) {
+            const uint32_t x = v[w];
+#pragma unroll 8
+            for (int j = 0; j < 32; j++) {
+                const uint32_t m = 0u - ((x >> j) & 1u);
+                const uint4 r0 = s_row[32 * w + j][0];
+                const uint32_t r1 = s_row[32 * w + j][1].x;
+                y0 ^= r0.x & m; y1 ^= r0.y & m; y2 ^= r0.z & m; y3 ^= r0.w & m; y4 ^= r1 & m;
+            }
+        }
+        v[0] = y0; v[1] = y1; v[2] = y2; v[3] = y3; v[4] = y4;
+    }
 }
 
 // ------------------------------------------------------------------ closest-hit shading (Shader.cu:94-242)
@@ -494,7 +527,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                              s->rng_cur_off == (uint64_t)fp->sample_offset;
         if (!cont_ok) {
             if (!base_ok) {
-                k_rng_init<<<div_up(npix, 128), 128, 0, st>>>(s->rng_base.p, npix, fp->seed,
+                k_rng_init<<<div_up(div_up(npix, kRngRun), 128), 128, 0, st>>>(s->rng_base.p, npix, fp->seed,
                                                               (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
                 s->launches += 1;
                 s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;

@@ -37,6 +37,38 @@ def xorwow_step(s):
     return np.array([d] + v, np.uint32), (v[4] + d) & 0xFFFFFFFF
 
 
+def test_sequence_skip_is_one_matvec_per_pixel(oracle):
+    """k_rng_init walks runs of consecutive pixels with state(p+1) = S * state(p), S = cuRAND's
+    precalc_xorwow_matrix[0] (GF(2) matrix, row i = image of state bit i); d is unchanged."""
+    hdr = "/usr/local/cuda/include/curand_precalc.h"
+    if not os.path.exists(hdr):
+        pytest.skip("CUDA toolkit headers absent")
+    txt = open(hdr).read()
+    body = txt[txt.index("precalc_xorwow_matrix[32][800]"):]
+    body = body[body.index("{") + 1:]
+    words = []
+    for tok in body.replace("{", " ").replace("}", " ").replace(",", " ").split():
+        if tok.endswith("U") or tok.endswith("UL"):
+            tok = tok.rstrip("UL")
+        try:
+            words.append(int(tok, 0))
+        except ValueError:
+            break
+        if len(words) == 800:
+            break
+    S = np.array(words, np.uint32).reshape(160, 5)
+    for seed, p0, off in [(1, 0, 0), (1234, 63, 64), (7, 8294399 - 5, 4096), (2 ** 40 + 3, 4095, 0)]:
+        s = oracle.xorwow_state(seed, p0, off)
+        for k in range(1, 6):
+            y = np.zeros(5, np.uint32)
+            for w in range(5):
+                for j in range(32):
+                    if (int(s[1 + w]) >> j) & 1:
+                        y ^= S[32 * w + j]
+            s = np.concatenate([s[:1], y])
+            assert np.array_equal(s, oracle.xorwow_state(seed, p0 + k, off)), (seed, p0, off, k)
+
+
 def test_register_xorwow_restatement(oracle):
     s = oracle.xorwow_state(99, 1234, 64)
     want = oracle.xorwow_uniforms(99, 1234, 64, 16)
