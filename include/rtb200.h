@@ -136,6 +136,10 @@ int rt_scene_add_spheres(rt_scene scene, const float *dev_centers, const float *
                          size_t count, uint32_t *group_out);
 int rt_scene_add_triangles(rt_scene scene, const float *dev_vertices, const float *dev_normals,
                            size_t count, uint32_t *group_out);
+/* Drop every geometry group and instance (materials and options stay): the scene of the next VTK
+ * file of a series is assembled from scratch while the device buffers of the accel are reused.  The
+ * reference keeps one IAS + SBT per file instead (RendererTime.cu:186-224, RendererMesh.cu:186-222). */
+int rt_scene_clear_geometry(rt_scene scene);
 /* Re-point an existing group at new buffers / a new count (per-frame particle data). */
 int rt_scene_update_group(rt_scene scene, uint32_t group, const float *dev_a, const float *dev_b,
                           size_t count);

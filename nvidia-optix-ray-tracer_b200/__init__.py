@@ -26,7 +26,7 @@ RT_RNG_SAMPLE_STRIDE = 64
 ABI_SYMBOLS = [
     "rt_abi_version", "rt_context_create", "rt_context_destroy", "rt_last_error",
     "rt_scene_create", "rt_scene_destroy", "rt_scene_set_option", "rt_scene_set_materials", "rt_scene_add_spheres",
-    "rt_scene_add_triangles", "rt_scene_update_group", "rt_scene_add_instance",
+    "rt_scene_add_triangles", "rt_scene_clear_geometry", "rt_scene_update_group", "rt_scene_add_instance",
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
@@ -94,6 +94,7 @@ def lib() -> C.CDLL:
         L.rt_scene_set_materials.argtypes = [vp, vp, sz, vp, sz]
         L.rt_scene_add_spheres.argtypes = [vp, vp, vp, sz, C.POINTER(u32)]
         L.rt_scene_add_triangles.argtypes = [vp, vp, vp, sz, C.POINTER(u32)]
+        L.rt_scene_clear_geometry.argtypes = [vp]
         L.rt_scene_update_group.argtypes = [vp, u32, vp, vp, sz]
         L.rt_scene_add_instance.argtypes = [vp, u32, vp, C.c_int, u32, u32, C.POINTER(u32)]
         L.rt_scene_set_transforms.argtypes = [vp, vp, sz, sz, vp]
@@ -202,6 +203,9 @@ class Scene:
         g = C.c_uint32()
         self.ctx.check(lib().rt_scene_add_triangles(self._h, verts_ptr, normals_ptr, count, C.byref(g)))
         return g.value
+
+    def clear_geometry(self):
+        self.ctx.check(lib().rt_scene_clear_geometry(self._h))
 
     def update_group(self, group, a_ptr, b_ptr, count):
         self.ctx.check(lib().rt_scene_update_group(self._h, group, a_ptr, b_ptr, count))

@@ -184,6 +184,14 @@ int rt_scene_add_spheres(rt_scene scene, const float *dev_centers, const float *
 int rt_scene_add_triangles(rt_scene scene, const float *dev_vertices, const float *dev_normals, size_t count, uint32_t *group_out) {
     return add_group(scene, dev_vertices, dev_normals, count, 1, group_out);
 }
+int rt_scene_clear_geometry(rt_scene scene) {
+    if (!scene) return RT_ERR_INVALID;
+    Scene &s = scene->s;
+    s.groups.clear();
+    s.insts.clear();
+    s.built = false;
+    return RT_OK;
+}
 int rt_scene_update_group(rt_scene scene, uint32_t group, const float *a, const float *b, size_t count) {
     if (!scene) return RT_ERR_INVALID;
     Scene &s = scene->s;
