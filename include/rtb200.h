@@ -118,9 +118,9 @@ int rt_abi_version(void);
 int rt_scene_create(rt_context ctx, rt_scene *out);
 int rt_scene_destroy(rt_scene scene);
 /* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "wide" (1 = traverse
- * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf: 1..8,
- * capped at 3 under "wide"; 0 = auto: 1 under "wide", 4 under the binary tree), "batch_spp" (samples per pixel in flight per wavefront batch),
- * "t1" / "t2" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
+ * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf of
+ * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch),
+ * "t1" / "t2" / "t3" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
  * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel). */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 

@@ -265,80 +265,60 @@ k_morton(const float4 *__restrict__ w_geom, const float4 *__restrict__ tri_v12, 
 }
 
 // ------------------------------------------------------------------ K4: LSD radix sort, 8-bit digits
+// One-sweep organisation (Adinets & Merrill 2022): ONE histogram kernel reads the keys once and
+// counts all four digits; each of the four passes is then a single kernel in which a tile of 4096
+// keys ranks its keys, obtains the number of equal-digit keys in the tiles before it by a decoupled
+// look-back over per-tile status words (flag + count in one 32-bit word), and scatters.  Tiles take
+// their index from an atomic ticket so that a tile only ever waits for tiles that already run.
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 keys per block
+constexpr uint32_t kFlagAggregate = 1u << 30, kFlagPrefix = 2u << 30, kFlagMask = 3u << 30;
+// layout of the sort scratch buffer (u32 words): [4][256] digit histograms, [4] tickets, [4][ntiles][256] status
+__host__ __device__ inline size_t sort_scratch_words(uint32_t ntiles) { return 4 * 256 + 4 + 4 * (size_t)ntiles * 256; }
 
 __global__ void __launch_bounds__(kSortThreads)
-k_sort_hist(const uint32_t *__restrict__ keys, uint32_t n, int shift, uint32_t *__restrict__ ghist, uint32_t nblocks) {
-    __shared__ uint32_t h[256];
-    h[threadIdx.x] = 0;
+k_sort_hist(const uint32_t *__restrict__ keys, uint32_t n, uint32_t *__restrict__ ghist) {
+    __shared__ uint32_t h[4][256];
+    for (int i = threadIdx.x; i < 4 * 256; i += kSortThreads) (&h[0][0])[i] = 0;
     __syncthreads();
     const uint32_t base = blockIdx.x * kSortTile;
-#pragma unroll
+#pragma unroll 4
     for (int j = 0; j < kSortItems; j++) {
         const uint32_t i = base + j * kSortThreads + threadIdx.x;
-        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+        if (i < n) {
+            const uint32_t k = keys[i];
+            atomicAdd(&h[0][k & 255u], 1u);
+            atomicAdd(&h[1][(k >> 8) & 255u], 1u);
+            atomicAdd(&h[2][(k >> 16) & 255u], 1u);
+            atomicAdd(&h[3][k >> 24], 1u);
+        }
     }
     __syncthreads();
-    ghist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
-}
-
-// exclusive scan of `total` counters by one 1024-thread block (the table is small: 256 per tile)
-__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *__restrict__ g, uint32_t total) {
-    __shared__ uint32_t warp_sum[32];
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    // coalesced tiles of 1024*4 counters, carried sequentially
-    for (uint32_t base = 0; base < total; base += 4096u) {
-        const uint32_t i0 = base + threadIdx.x * 4u;
-        uint32_t v[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) v[k] = (i0 + k < total) ? g[i0 + k] : 0u;
-        const uint32_t s = v[0] + v[1] + v[2] + v[3];
-        uint32_t inc = s;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
-            if (lane >= (uint32_t)o) inc += t;
-        }
-        if (lane == 31) warp_sum[wid] = inc;
-        __syncthreads();
-        if (wid == 0) {
-            uint32_t w = warp_sum[lane];
-            uint32_t winc = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, winc, o);
-                if (lane >= (uint32_t)o) winc += t;
-            }
-            warp_sum[lane] = winc - w;  // exclusive
-        }
-        __syncthreads();
-        uint32_t ex = carry + warp_sum[wid] + (inc - s);
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if (i0 + k < total) g[i0 + k] = ex;
-            ex += v[k];
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = ex;
-        __syncthreads();
+    for (int i = threadIdx.x; i < 4 * 256; i += kSortThreads) {
+        const uint32_t v = (&h[0][0])[i];
+        if (v) atomicAdd(ghist + i, v);
     }
 }
 
 __global__ void __launch_bounds__(kSortThreads)
-k_sort_scatter(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-               uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int shift,
-               const uint32_t *__restrict__ ghist, uint32_t nblocks) {
+k_sort_pass(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+            uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int pass,
+            uint32_t *__restrict__ scratch, uint32_t ntiles) {
     __shared__ uint32_t cnt[8][256];
+    __shared__ uint32_t s_digit_base[256];
+    __shared__ uint32_t s_tile;
+    const uint32_t *ghist = scratch + 256 * pass;
+    uint32_t *ticket = scratch + 4 * 256 + pass;
+    volatile uint32_t *status = scratch + 4 * 256 + 4 + (size_t)pass * ntiles * 256;
+    const int shift = 8 * pass;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     for (int i = threadIdx.x; i < 8 * 256; i += kSortThreads) (&cnt[0][0])[i] = 0;
     __syncthreads();
+    const uint32_t tile = s_tile;
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    const uint32_t base = blockIdx.x * kSortTile + w * (kSortTile / 8);
+    const uint32_t base = tile * kSortTile + w * (kSortTile / 8);
     uint32_t key[kSortItems];
     uint16_t rank[kSortItems];
 #pragma unroll
@@ -360,14 +340,39 @@ k_sort_scatter(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict_
     }
     __syncthreads();
     {
+        // thread dg: per-warp exclusive offsets inside the tile, tile total, look-back, global base
         const uint32_t dg = threadIdx.x;
-        uint32_t run = ghist[dg * nblocks + blockIdx.x];
+        uint32_t run = 0;
 #pragma unroll
         for (int ww = 0; ww < 8; ww++) {
             const uint32_t t = cnt[ww][dg];
             cnt[ww][dg] = run;
             run += t;
         }
+        const uint32_t total = run;
+        if (tile + 1 < ntiles) status[(size_t)tile * 256 + dg] = (tile == 0 ? kFlagPrefix : kFlagAggregate) | total;
+        uint32_t excl = 0;
+        for (int t = (int)tile - 1; t >= 0;) {
+            const uint32_t v = status[(size_t)t * 256 + dg];
+            if (!(v & kFlagMask)) continue;  // not published yet: tile t runs (it holds an earlier ticket)
+            excl += v & ~kFlagMask;
+            if (v & kFlagPrefix) break;
+            t--;
+        }
+        if (tile > 0 && tile + 1 < ntiles) status[(size_t)tile * 256 + dg] = kFlagPrefix | (excl + total);
+        // exclusive prefix of the global digit histogram (256 bins: one warp-scan per 32, then 8 partial sums)
+        uint32_t g = ghist[dg], inc = g;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (lane == 31) s_digit_base[w] = inc;  // warp totals, reused below
+        __syncthreads();
+        uint32_t wbase = 0;
+        for (uint32_t ww = 0; ww < w; ww++) wbase += s_digit_base[ww];
+        __syncthreads();
+        s_digit_base[dg] = wbase + inc - g + excl;
     }
     __syncthreads();
 #pragma unroll
@@ -375,7 +380,7 @@ k_sort_scatter(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict_
         const uint32_t i = base + c * 32 + lane;
         if (i < n) {
             const uint32_t dg = (key[c] >> shift) & 255u;
-            const uint32_t pos = cnt[w][dg] + rank[c];
+            const uint32_t pos = s_digit_base[dg] + cnt[w][dg] + rank[c];
             keys_out[pos] = key[c];
             vals_out[pos] = vals_in[i];
         }
@@ -480,13 +485,54 @@ k_refit(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12
     }
 }
 
-// padded boxes of the outlier primitives (tested after the tree walk, culled by these boxes)
+// padded boxes of the outlier primitives (tested after the tree walk, culled by these boxes) and the
+// "free box": the tree's bounds clipped, one outlier at a time, along the axis that keeps most of it,
+// so that no outlier box reaches inside.  Segments inside the free box skip the outlier list.
 __global__ void k_huge_boxes(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info) {
     const uint32_t k = threadIdx.x;
-    if (k >= info->n_huge) return;
-    const Box3 b = pad_box(prim_box(slot_geom[info->n_bvh + k], tri_v12));
-    info->huge_lo[k][0] = b.lo.x; info->huge_lo[k][1] = b.lo.y; info->huge_lo[k][2] = b.lo.z;
-    info->huge_hi[k][0] = b.hi.x; info->huge_hi[k][1] = b.hi.y; info->huge_hi[k][2] = b.hi.z;
+    const uint32_t nh = info->n_huge;
+    if (k < nh) {
+        const Box3 b = pad_box(prim_box(slot_geom[info->n_bvh + k], tri_v12));
+        info->huge_lo[k][0] = b.lo.x; info->huge_lo[k][1] = b.lo.y; info->huge_lo[k][2] = b.lo.z;
+        info->huge_hi[k][0] = b.hi.x; info->huge_hi[k][1] = b.hi.y; info->huge_hi[k][2] = b.hi.z;
+    }
+    __syncthreads();
+    if (k != 0) return;
+    float lo[3], hi[3];
+    bool empty = info->n_bvh == 0;
+    for (int a = 0; a < 3; a++) {
+        lo[a] = info->scene_lo[a];
+        hi[a] = info->scene_hi[a];
+    }
+    for (uint32_t h = 0; h < nh && !empty; h++) {
+        const float *bl = info->huge_lo[h], *bh = info->huge_hi[h];
+        bool overlap = true;
+        for (int a = 0; a < 3; a++) overlap = overlap && bl[a] < hi[a] && bh[a] > lo[a];
+        if (!overlap) continue;
+        int best_axis = -1, best_side = 0;
+        float best_keep = 0.0f;
+        for (int a = 0; a < 3; a++) {
+            const float ext = hi[a] - lo[a];
+            if (!(ext > 0.0f)) continue;
+            if (bl[a] > lo[a]) {  // keep [lo, box.lo]
+                const float keep = (bl[a] - lo[a]) / ext;
+                if (keep > best_keep) { best_keep = keep; best_axis = a; best_side = 0; }
+            }
+            if (bh[a] < hi[a]) {  // keep [box.hi, hi]
+                const float keep = (hi[a] - bh[a]) / ext;
+                if (keep > best_keep) { best_keep = keep; best_axis = a; best_side = 1; }
+            }
+        }
+        if (best_axis < 0) empty = true;
+        else if (best_side == 0) hi[best_axis] = bl[best_axis];
+        else lo[best_axis] = bh[best_axis];
+    }
+    for (int a = 0; a < 3; a++) {
+        // margin: dominates the fp32 rounding of the segment end point o + t*d
+        const float m = 6.1035156e-5f * fmaxf(fmaxf(fabsf(lo[a]), fabsf(hi[a])), hi[a] - lo[a]) + 1e-30f;
+        info->free_lo[a] = empty ? 1.0f : lo[a] + m;
+        info->free_hi[a] = empty ? -1.0f : hi[a] - m;
+    }
 }
 
 // n_bvh <= 1: the root is the only node
@@ -633,7 +679,8 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
         used |= 1u << sl;
         child_at[sl] = i;
     }
-    uint32_t imask = 0, n_int = 0, n_pr = 0;
+    // every leaf of the binary tree holds exactly one primitive under the wide tree (build_accel)
+    uint32_t imask = 0, leafmask = 0, n_int = 0, n_pr = 0;
     for (int k = 0; k < 8; k++) {
         const int i = child_at[k];
         if (i < 0) continue;
@@ -641,44 +688,37 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
             imask |= 1u << k;
             n_int += 1;
         } else {
-            n_pr += (((uint32_t)ch[i].enc >> kLeafCountShift) & 7u) + 1u;
+            leafmask |= 1u << k;
+            n_pr += 1;
         }
     }
     const uint32_t child_base = n_int ? atomicAdd(&info->n_wnodes, n_int) : 0u;
     const uint32_t prim_base = n_pr ? atomicAdd(&info->n_wprims, n_pr) : 0u;
-    uint32_t meta[8], px[2] = {0, 0}, py[2] = {0, 0}, pz[2] = {0, 0}, hx[2] = {0, 0}, hy[2] = {0, 0}, hz[2] = {0, 0};
+    uint32_t px[2] = {0, 0}, py[2] = {0, 0}, pz[2] = {0, 0}, hx[2] = {0, 0}, hy[2] = {0, 0}, hz[2] = {0, 0};
     uint32_t rank = 0, off = 0;
     for (int k = 0; k < 8; k++) {
         const int i = child_at[k];
         const int sh = 8 * (k & 3);
         if (i < 0) {  // empty slot: inverted box, never hit
-            meta[k] = 0;
             px[k >> 2] |= 255u << sh; py[k >> 2] |= 255u << sh; pz[k >> 2] |= 255u << sh;
             continue;
         }
         px[k >> 2] |= (uint32_t)qlo[0][i] << sh; py[k >> 2] |= (uint32_t)qlo[1][i] << sh; pz[k >> 2] |= (uint32_t)qlo[2][i] << sh;
         hx[k >> 2] |= (uint32_t)qhi[0][i] << sh; hy[k >> 2] |= (uint32_t)qhi[1][i] << sh; hz[k >> 2] |= (uint32_t)qhi[2][i] << sh;
         if (ch[i].enc >= 0) {
-            meta[k] = 0x20u | (24u + (uint32_t)k);
             wtask[child_base + rank] = (uint32_t)ch[i].enc;
             rank += 1;
         } else {
-            const uint32_t enc = (uint32_t)ch[i].enc;
-            const uint32_t c = ((enc >> kLeafCountShift) & 7u) + 1u, f = enc & kLeafFirstMask;
-            meta[k] = (((1u << c) - 1u) << 5) | off;
-            for (uint32_t t = 0; t < c; t++) {
-                wslot_geom[prim_base + off + t] = slot_geom[f + t];
-                wslot_prim[prim_base + off + t] = slot_prim[f + t];
-                wslot_mat[prim_base + off + t] = slot_mat[f + t];
-            }
-            off += c;
+            const uint32_t f = (uint32_t)ch[i].enc & kLeafFirstMask;
+            wslot_geom[prim_base + off] = slot_geom[f];
+            wslot_prim[prim_base + off] = slot_prim[f];
+            wslot_mat[prim_base + off] = slot_mat[f];
+            off += 1;
         }
     }
     float4 *o = reinterpret_cast<float4 *>(wnodes + w);
     o[0] = make_float4(org[0], org[1], org[2], __uint_as_float(eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24)));
-    o[1] = make_float4(__uint_as_float(child_base), __uint_as_float(prim_base),
-                       __uint_as_float(meta[0] | (meta[1] << 8) | (meta[2] << 16) | (meta[3] << 24)),
-                       __uint_as_float(meta[4] | (meta[5] << 8) | (meta[6] << 16) | (meta[7] << 24)));
+    o[1] = make_float4(__uint_as_float(child_base), __uint_as_float(prim_base), __uint_as_float(leafmask), 0.0f);
     o[2] = make_float4(__uint_as_float(px[0]), __uint_as_float(px[1]), __uint_as_float(py[0]), __uint_as_float(py[1]));
     o[3] = make_float4(__uint_as_float(pz[0]), __uint_as_float(pz[1]), __uint_as_float(hx[0]), __uint_as_float(hx[1]));
     o[4] = make_float4(__uint_as_float(hy[0]), __uint_as_float(hy[1]), __uint_as_float(hz[0]), __uint_as_float(hz[1]));
@@ -771,7 +811,7 @@ int build_accel(Scene *s, cudaStream_t st) {
         RT_CUDA(ctx, s->keys[k].reserve(n1, &s->bytes));
         RT_CUDA(ctx, s->vals[k].reserve(n1, &s->bytes));
     }
-    RT_CUDA(ctx, s->sort_hist.reserve(256 * (size_t)sort_blocks, &s->bytes));
+    RT_CUDA(ctx, s->sort_hist.reserve(sort_scratch_words(sort_blocks), &s->bytes));
     RT_CUDA(ctx, s->bucket_tab.reserve(kExtentBuckets * 8, &s->bytes));
     RT_CUDA(ctx, s->nodes.reserve(n1, &s->bytes));
     RT_CUDA(ctx, s->parent_int.reserve(n1, &s->bytes));
@@ -807,19 +847,19 @@ int build_accel(Scene *s, cudaStream_t st) {
     if (n) {
         k_morton<<<gb, 256, 0, st>>>(s->w_geom.p, s->tri_v12.p, n, s->info.p, s->keys[0].p, s->vals[0].p);
         s->launches += 1;
+        RT_CUDA(ctx, cudaMemsetAsync(s->sort_hist.p, 0, sort_scratch_words(sort_blocks) * sizeof(uint32_t), st));
+        k_sort_hist<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[0].p, n, s->sort_hist.p);
+        s->launches += 1;
         int src = 0;
         for (int pass = 0; pass < 4; pass++) {
-            const int shift = 8 * pass;
-            k_sort_hist<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[src].p, n, shift, s->sort_hist.p, sort_blocks);
-            k_sort_scan<<<1, 1024, 0, st>>>(s->sort_hist.p, 256u * sort_blocks);
-            k_sort_scatter<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[src].p, s->vals[src].p, s->keys[src ^ 1].p,
-                                                                 s->vals[src ^ 1].p, n, shift, s->sort_hist.p, sort_blocks);
+            k_sort_pass<<<sort_blocks, kSortThreads, 0, st>>>(s->keys[src].p, s->vals[src].p, s->keys[src ^ 1].p,
+                                                              s->vals[src ^ 1].p, n, pass, s->sort_hist.p, sort_blocks);
             src ^= 1;
-            s->launches += 3;
+            s->launches += 1;
         }
         // 4 passes: result back in buffer 0
         k_gather<<<gb, 256, 0, st>>>(s->vals[0].p, s->w_geom.p, s->w_mat.p, n, s->slot_geom.p, s->slot_prim.p, s->slot_mat.p);
-        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? (s->leaf_max ? std::min(s->leaf_max, kWideLeafMax) : 1u) : (s->leaf_max ? s->leaf_max : 4u)));
+        k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? 1u : (s->leaf_max ? s->leaf_max : 4u)));
         k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
         s->launches += 3;
     }

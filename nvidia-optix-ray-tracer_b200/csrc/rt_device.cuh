@@ -327,9 +327,10 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 
 // ------------------------------------------------------------------ 8-wide compressed BVH traversal
 // Same two-phase warp scheme as extend_warp, over WNode (rt_internal.h).  A lane keeps
-//   (gbase, gmask): current node group = child_base + [31:24] pending internal-child hits placed at
-//                   their traversal priority (slot ^ octinv, nearer octant = higher bit), [7:0] imask;
-//   (pbase, pmask), (pbase2, pmask2): up to two postponed primitive groups (bit k = prim_base + k).
+//   (gbase, gmask): current node group = child_base, [7:0] imask of the node, [15:8] pending internal-child
+//                   hits at their traversal priority (slot ^ octant, nearer octant = higher bit);
+//   (pbase, pmask), (pbase2, pmask2): up to two postponed primitive groups, [15:0] = which slots hold a
+//                   primitive (primitive of slot b = pbase + popc(present below b)), [31:16] pending hits.
 // The stack holds node groups only (8 bytes each).  Children are visited in octant order, which is
 // a heuristic only: every hit child is eventually visited, so the closest hit equals brute force.
 #define RT_WSTACK 64
@@ -345,19 +346,37 @@ __device__ __forceinline__ float qfloat(uint32_t w, uint32_t magic) {
     asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x7650 + J));
     return __uint_as_float(r);
 }
-// per byte: 0xFF if its sign bit is set, else 0x00 (prmt selector msb = replicate the sign of the byte;
-// __byte_perm() only honours 3 selector bits, so this is spelled in PTX)
-__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
-    uint32_t r;
-    asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(r) : "r"(x));
+
+// Blackwell packed fp32: two fused multiply-adds per issue slot (FFMA2).  (d0, d1) = (a0, a1) * s + b
+// with s and b given as register pairs holding the same value twice.
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
     return r;
 }
+__device__ __forceinline__ void ffma2(float &d0, float &d1, float a0, float a1, unsigned long long s2, unsigned long long b2) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(pack2(a0, a1)), "l"(s2), "l"(b2));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
 
-#define QF(w, j) ((j) == 0 ? qfloat<0>(w, magic) : (j) == 1 ? qfloat<1>(w, magic) : (j) == 2 ? qfloat<2>(w, magic) : qfloat<3>(w, magic))
+// s_perm[o][m]: the 8-bit child mask m (slot order) permuted to traversal priority for ray octant o,
+// bit (j ^ o) of the result = bit j of m.  2 KB of shared memory, filled by every block at start.
+__device__ __forceinline__ void fill_perm_table(uint8_t (*s_perm)[256]) {
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) {
+        const uint32_t o = i >> 8, m = i & 255u;
+        uint32_t r = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) r |= ((m >> j) & 1u) << (j ^ o);
+        s_perm[o][m] = (uint8_t)r;
+    }
+    __syncthreads();
+}
 
 // `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
 __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
-                                                 float4 *__restrict__ hits, int t1, int t2, int fetch_min, uint32_t magic) {
+                                                 float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic,
+                                                 const uint8_t (*s_perm)[256]) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt = (1u << lane) - 1u;
@@ -369,12 +388,11 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
     uint2 stack[RT_WSTACK];
     int sp = 0;
     uint32_t gbase = 0, gmask = 0, pbase = 0, pmask = 0, pbase2 = 0, pmask2 = 0;
-    bool huge_done = true;
-    uint32_t idx = 0, skip_slot = kNoSlot, octinv = 0;
-    Ray r;
-    r.o = r.d = f3(0, 0, 0);
-    r.tmin = RT_ZERO;
-    r.tmax = RT_INF;
+    bool huge_done = true, huge_wait = false;
+    uint32_t idx = 0, skip_slot = kNoSlot, oct = 0;
+    // origin and direction are NOT kept in registers: the node test only needs 1/d and -o/d, the
+    // primitive tests re-read the ray from the queue (an L1/L2 hit), which keeps the kernel at 64 registers
+    float tmin = RT_ZERO, tmax = RT_INF;
     Hit best;
     best.t = 0.0f;
     best.slot = kNoSlot;
@@ -394,34 +412,33 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
             if (!alive && i < n) {
                 const float4 o4 = in.o[i], d4 = in.d[i];
                 idx = i;
-                r.o = f3(o4.x, o4.y, o4.z);
-                r.d = f3(d4.x, d4.y, d4.z);
+                const F3 rd = f3(d4.x, d4.y, d4.z);
                 if (in.skip) {
-                    r.tmin = o4.w;
-                    r.tmax = d4.w;
+                    tmin = o4.w;
+                    tmax = d4.w;
                     skip_slot = in.skip[i];
                 } else {
-                    r.tmin = RT_ZERO;  // Shader.cu:231-233, 264-267
-                    r.tmax = RT_INF;
+                    tmin = RT_ZERO;  // Shader.cu:231-233, 264-267
+                    tmax = RT_INF;
                     skip_slot = __float_as_uint(d4.w);
                 }
-                best.t = r.tmax;
+                best.t = tmax;
                 best.slot = kNoSlot;
                 best.u = best.v = 0.0f;
-                a = dot(r.d, r.d);
+                a = dot(rd, rd);
                 inv_a = 1.0f / a;
-                const float ex = fabsf(r.d.x) < 1e-30f ? copysignf(1e-30f, r.d.x) : r.d.x;
-                const float ey = fabsf(r.d.y) < 1e-30f ? copysignf(1e-30f, r.d.y) : r.d.y;
-                const float ez = fabsf(r.d.z) < 1e-30f ? copysignf(1e-30f, r.d.z) : r.d.z;
+                const float ex = fabsf(rd.x) < 1e-30f ? copysignf(1e-30f, rd.x) : rd.x;
+                const float ey = fabsf(rd.y) < 1e-30f ? copysignf(1e-30f, rd.y) : rd.y;
+                const float ez = fabsf(rd.z) < 1e-30f ? copysignf(1e-30f, rd.z) : rd.z;
                 ix = 1.0f / ex; iy = 1.0f / ey; iz = 1.0f / ez;
-                ox = -r.o.x * ix; oy = -r.o.y * iy; oz = -r.o.z * iz;
-                octinv = (ix >= 0.0f ? 1u : 0u) | (iy >= 0.0f ? 2u : 0u) | (iz >= 0.0f ? 4u : 0u);
-                octinv *= 0x01010101u;  // replicated per byte for the 4-children-at-a-time mask maths
+                ox = -o4.x * ix; oy = -o4.y * iy; oz = -o4.z * iz;
+                oct = (ix >= 0.0f ? 1u : 0u) | (iy >= 0.0f ? 2u : 0u) | (iz >= 0.0f ? 4u : 0u);
                 huge_done = n_huge == 0;
+                huge_wait = false;
                 sp = 0;
                 pmask = pmask2 = 0;
                 gbase = 0;
-                gmask = have_tree ? 0x80000000u : 0u;  // root: slot 7^octinv of an imask-0 group -> index 0
+                gmask = have_tree ? 0x8000u : 0u;  // root: slot 7^oct of an imask-0 group -> index 0
                 alive = true;
             }
         }
@@ -430,22 +447,22 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
         // ---- phase 1: wide nodes
         bool first = true;
         for (;;) {
-            const bool want = alive && pmask2 == 0 && ((gmask >> 24) != 0 || sp > 0);
+            const bool want = alive && (pmask2 >> 16) == 0 && ((gmask >> 8) != 0 || sp > 0);
             const uint32_t mw = __ballot_sync(FULL, want);
             if (!mw) break;
-            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && pmask != 0)) break;
+            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && (pmask >> 16) != 0)) break;
             first = false;
             if (want) {
-                if ((gmask >> 24) == 0) {
+                if ((gmask >> 8) == 0) {
                     const uint2 e = stack[--sp];
                     gbase = e.x;
                     gmask = e.y;
                 }
                 const uint32_t bit = 31u - (uint32_t)__clz(gmask);
                 gmask &= ~(1u << bit);
-                const uint32_t slot = (bit - 24u) ^ (octinv & 7u);
+                const uint32_t slot = (bit - 8u) ^ oct;
                 const uint32_t child = gbase + __popc(gmask & ((1u << slot) - 1u));
-                if (gmask >> 24) stack[sp++] = make_uint2(gbase, gmask);
+                if (gmask >> 8) stack[sp++] = make_uint2(gbase, gmask);
 
                 const float4 *q = wn + 5 * (size_t)child;
                 const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
@@ -457,8 +474,10 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
                 const float bx = __fmaf_rn(-8388608.0f, sx, __fmaf_rn(w0.x, ix, ox));
                 const float by = __fmaf_rn(-8388608.0f, sy, __fmaf_rn(w0.y, iy, oy));
                 const float bz = __fmaf_rn(-8388608.0f, sz, __fmaf_rn(w0.z, iz, oz));
+                const unsigned long long sx2 = pack2(sx, sx), sy2 = pack2(sy, sy), sz2 = pack2(sz, sz);
+                const unsigned long long bx2 = pack2(bx, bx), by2 = pack2(by, by), bz2 = pack2(bz, bz);
                 const bool px = ix >= 0.0f, py = iy >= 0.0f, pz = iz >= 0.0f;
-                uint32_t hitmask = 0;
+                uint32_t hm = 0;  // bit j = child slot j hit
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     const uint32_t lox = __float_as_uint(h ? w2.y : w2.x), loy = __float_as_uint(h ? w2.w : w2.z);
@@ -467,32 +486,43 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
                     const uint32_t nx = px ? lox : hix, fx = px ? hix : lox;
                     const uint32_t ny = py ? loy : hiy, fy = py ? hiy : loy;
                     const uint32_t nz = pz ? loz : hiz, fz = pz ? hiz : loz;
-                    // per byte: which bit of the hit mask a child owns and how many bits (leaf = unary count)
-                    const uint32_t meta4 = __float_as_uint(h ? w1.w : w1.z);
-                    const uint32_t inner4 = sign_extend_s8x4(((meta4 & (meta4 << 1)) & 0x10101010u) << 3);
-                    const uint32_t bit4 = (meta4 ^ (octinv & inner4 & 0x07070707u)) & 0x1F1F1F1Fu;
-                    const uint32_t cnt4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const float tnx = __fmaf_rn(QF(nx, j), sx, bx), tfx = __fmaf_rn(QF(fx, j), sx, bx);
-                        const float tny = __fmaf_rn(QF(ny, j), sy, by), tfy = __fmaf_rn(QF(fy, j), sy, by);
-                        const float tnz = __fmaf_rn(QF(nz, j), sz, bz), tfz = __fmaf_rn(QF(fz, j), sz, bz);
-                        const float tlo = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, r.tmin));
-                        const float thi = fminf(fminf(tfx, tfy), fminf(tfz, best.t));
-                        if (tlo <= thi * 1.000002f)  // empty slots have count bits 0 and an inverted box
-                            hitmask |= ((cnt4 >> (8 * j)) & 0xFFu) << ((bit4 >> (8 * j)) & 0xFFu);
+                    for (int jp = 0; jp < 2; jp++) {
+                        float tnx[2], tfx[2], tny[2], tfy[2], tnz[2], tfz[2];
+                        if (jp == 0) {
+                            ffma2(tnx[0], tnx[1], qfloat<0>(nx, magic), qfloat<1>(nx, magic), sx2, bx2);
+                            ffma2(tfx[0], tfx[1], qfloat<0>(fx, magic), qfloat<1>(fx, magic), sx2, bx2);
+                            ffma2(tny[0], tny[1], qfloat<0>(ny, magic), qfloat<1>(ny, magic), sy2, by2);
+                            ffma2(tfy[0], tfy[1], qfloat<0>(fy, magic), qfloat<1>(fy, magic), sy2, by2);
+                            ffma2(tnz[0], tnz[1], qfloat<0>(nz, magic), qfloat<1>(nz, magic), sz2, bz2);
+                            ffma2(tfz[0], tfz[1], qfloat<0>(fz, magic), qfloat<1>(fz, magic), sz2, bz2);
+                        } else {
+                            ffma2(tnx[0], tnx[1], qfloat<2>(nx, magic), qfloat<3>(nx, magic), sx2, bx2);
+                            ffma2(tfx[0], tfx[1], qfloat<2>(fx, magic), qfloat<3>(fx, magic), sx2, bx2);
+                            ffma2(tny[0], tny[1], qfloat<2>(ny, magic), qfloat<3>(ny, magic), sy2, by2);
+                            ffma2(tfy[0], tfy[1], qfloat<2>(fy, magic), qfloat<3>(fy, magic), sy2, by2);
+                            ffma2(tnz[0], tnz[1], qfloat<2>(nz, magic), qfloat<3>(nz, magic), sz2, bz2);
+                            ffma2(tfz[0], tfz[1], qfloat<2>(fz, magic), qfloat<3>(fz, magic), sz2, bz2);
+                        }
+#pragma unroll
+                        for (int e = 0; e < 2; e++) {
+                            const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], tmin));
+                            const float thi = fminf(fminf(tfx[e], tfy[e]), fminf(tfz[e], best.t));
+                            if (tlo <= thi * 1.000002f) hm |= 1u << (4 * h + 2 * jp + e);  // empty slots hold an inverted box
+                        }
                     }
                 }
+                const uint32_t imask = eim >> 24, leafmask = __float_as_uint(w1.z) & 0xFFu;
                 gbase = __float_as_uint(w1.x);
-                gmask = (hitmask & 0xFF000000u) | (eim >> 24);
-                const uint32_t pm = hitmask & 0x00FFFFFFu;
+                gmask = imask | ((uint32_t)s_perm[oct][hm & imask] << 8);
+                const uint32_t pm = hm & leafmask;
                 if (pm) {
-                    if (pmask == 0) {
+                    if ((pmask >> 16) == 0) {
                         pbase = __float_as_uint(w1.y);
-                        pmask = pm;
+                        pmask = leafmask | (pm << 16);
                     } else {
                         pbase2 = __float_as_uint(w1.y);
-                        pmask2 = pm;
+                        pmask2 = leafmask | (pm << 16);
                     }
                 }
             }
@@ -501,18 +531,24 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
         // ---- phase 2: postponed primitives, one per iteration
         first = true;
         for (;;) {
-            const bool hl = alive && pmask != 0;
+            const bool hl = alive && (pmask >> 16) != 0;
             const uint32_t ml = __ballot_sync(FULL, hl);
             if (!ml) break;
             if (!first && __popc(ml) < t2 &&
-                __any_sync(FULL, alive && pmask2 == 0 && ((gmask >> 24) != 0 || sp > 0)))
+                __any_sync(FULL, alive && (pmask2 >> 16) == 0 && ((gmask >> 8) != 0 || sp > 0)))
                 break;
             first = false;
             if (hl) {
-                const uint32_t b = (uint32_t)__ffs(pmask) - 1u;
-                pmask &= pmask - 1u;
-                test_slot(sc, r, a, inv_a, pbase + b, skip_slot, best);
-                if (pmask == 0 && pmask2 != 0) {
+                const uint32_t b = (uint32_t)__ffs(pmask >> 16) - 1u;
+                pmask &= ~(0x10000u << b);
+                const float4 o4 = in.o[idx], d4 = in.d[idx];
+                Ray r;
+                r.o = f3(o4.x, o4.y, o4.z);
+                r.d = f3(d4.x, d4.y, d4.z);
+                r.tmin = tmin;
+                r.tmax = tmax;
+                test_slot(sc, r, a, inv_a, pbase + __popc(pmask & ((1u << b) - 1u)), skip_slot, best);
+                if ((pmask >> 16) == 0 && (pmask2 >> 16) != 0) {
                     pbase = pbase2;
                     pmask = pmask2;
                     pmask2 = 0;
@@ -520,24 +556,47 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
             }
         }
 
-        // ---- rays whose tree walk is over: outlier primitives (BuildInfo.huge_*), culled by their boxes
-        //      against the closest hit found so far, go through phase 2 as one last primitive group
-        if (alive && !huge_done && (gmask >> 24) == 0 && sp == 0 && pmask == 0) {
-            huge_done = true;
-            uint32_t m = 0;
-            for (uint32_t k = 0; k < n_huge; k++) {
-                const float x0 = __fmaf_rn(info->huge_lo[k][0], ix, ox), x1 = __fmaf_rn(info->huge_hi[k][0], ix, ox);
-                const float y0 = __fmaf_rn(info->huge_lo[k][1], iy, oy), y1 = __fmaf_rn(info->huge_hi[k][1], iy, oy);
-                const float z0 = __fmaf_rn(info->huge_lo[k][2], iz, oz), z1 = __fmaf_rn(info->huge_hi[k][2], iz, oz);
-                const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
-                const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best.t));
-                if (tlo <= thi * 1.000002f) m |= 1u << k;
+        // ---- rays whose tree walk is over: outlier primitives (BuildInfo.huge_*).  A segment with both
+        //      ends inside the outlier-free box is done at once; the others wait (huge_wait) until at least
+        //      t3 lanes of the warp are in the same state or nothing else is left to do, then cull the
+        //      outliers by their boxes against the closest hit so far and queue the survivors for phase 2.
+        if (alive && !huge_done && !huge_wait && (gmask >> 8) == 0 && sp == 0 && (pmask >> 16) == 0) {
+            bool need = best.slot == kNoSlot;
+            if (!need) {
+                const float4 o4 = in.o[idx], d4 = in.d[idx];
+                const float ex = o4.x + best.t * d4.x, ey = o4.y + best.t * d4.y, ez = o4.z + best.t * d4.z;
+                const float l0 = info->free_lo[0], l1 = info->free_lo[1], l2 = info->free_lo[2];
+                const float h0 = info->free_hi[0], h1 = info->free_hi[1], h2 = info->free_hi[2];
+                const bool in_o = o4.x > l0 && o4.x < h0 && o4.y > l1 && o4.y < h1 && o4.z > l2 && o4.z < h2;
+                const bool in_e = ex > l0 && ex < h0 && ey > l1 && ey < h1 && ez > l2 && ez < h2;
+                need = !(in_o && in_e);
             }
-            pbase = info->huge_slot[0];
-            pmask = m;
+            huge_wait = need;
+            huge_done = !need;
+        }
+        {
+            const uint32_t m3 = __ballot_sync(FULL, alive && huge_wait);
+            if (m3 && (__popc(m3) >= t3 ||
+                       !__any_sync(FULL, alive && !huge_wait && ((gmask >> 8) != 0 || sp > 0 || (pmask >> 16) != 0)))) {
+                if (alive && huge_wait) {
+                    uint32_t m = 0;
+                    for (uint32_t k = 0; k < n_huge; k++) {
+                        const float x0 = __fmaf_rn(info->huge_lo[k][0], ix, ox), x1 = __fmaf_rn(info->huge_hi[k][0], ix, ox);
+                        const float y0 = __fmaf_rn(info->huge_lo[k][1], iy, oy), y1 = __fmaf_rn(info->huge_hi[k][1], iy, oy);
+                        const float z0 = __fmaf_rn(info->huge_lo[k][2], iz, oz), z1 = __fmaf_rn(info->huge_hi[k][2], iz, oz);
+                        const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+                        const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best.t));
+                        if (tlo <= thi * 1.000002f) m |= 1u << k;
+                    }
+                    pbase = info->huge_slot[0];
+                    pmask = 0xFFFFu | (m << 16);  // all kMaxHuge <= 16 slots present: primitive k = pbase + k
+                    huge_wait = false;
+                    huge_done = true;
+                }
+            }
         }
         // ---- retire finished rays
-        if (alive && huge_done && (gmask >> 24) == 0 && sp == 0 && pmask == 0) {
+        if (alive && huge_done && (gmask >> 8) == 0 && sp == 0 && (pmask >> 16) == 0) {
             hits[idx] = make_float4(best.slot == kNoSlot ? RT_INF : best.t, __uint_as_float(best.slot), best.u, best.v);
             alive = false;
         }

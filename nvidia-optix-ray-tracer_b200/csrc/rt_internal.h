@@ -47,18 +47,18 @@ struct alignas(16) Node {
 // "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs"), collapsed from the
 // binary LBVH every frame.  Five 128-bit words:
 //   w0 = origin.x origin.y origin.z  bits(ex | ey<<8 | ez<<16 | imask<<24)   (scale_a = 2^(e_a-127))
-//   w1 = bits(child_base) bits(prim_base) bits(meta[0..3]) bits(meta[4..7])
+//   w1 = bits(child_base) bits(prim_base) bits(leafmask) 0
 //   w2 = qlo_x[0..3] qlo_x[4..7] qlo_y[0..3] qlo_y[4..7]
 //   w3 = qlo_z[0..3] qlo_z[4..7] qhi_x[0..3] qhi_x[4..7]
 //   w4 = qhi_y[0..3] qhi_y[4..7] qhi_z[0..3] qhi_z[4..7]
-// child box a-axis = origin_a + q * scale_a.  meta[i]: 0 = empty slot; internal child: 0x20 | (24+i);
-// leaf: (unary(count 1..3) << 5) | offset of its first primitive from prim_base (0..23).
+// child box a-axis = origin_a + q * scale_a.  Slot k is an internal child (bit k of imask), a leaf of
+// exactly ONE primitive (bit k of leafmask) or empty (neither; its quantised box is inverted).
 // Internal children are stored contiguously from child_base in slot order; the leaf primitives of a
-// node are contiguous from prim_base in slot order (primitives are re-packed per wide node).
+// node are contiguous from prim_base in slot order (primitives are re-packed per wide node), so the
+// child / primitive of slot k sits at base + popc(mask & ((1 << k) - 1)).
 struct alignas(16) WNode {
     float4 w0, w1, w2, w3, w4;
 };
-constexpr uint32_t kWideLeafMax = 3;
 
 constexpr uint32_t kLeafFlag = 0x80000000u;
 constexpr uint32_t kLeafFirstMask = 0x07FFFFFFu;
@@ -82,6 +82,10 @@ struct BuildInfo {
     uint32_t n_wprims;               // primitives re-packed by the collapse
     uint32_t level_end;              // collapse: end of the current level in the task queue
     uint32_t pad_;
+    // Box that no outlier primitive's padded box reaches into (shrunk by a safety margin): a ray
+    // segment whose two end points lie inside it cannot hit an outlier, so their tests are skipped.
+    float free_lo[3], free_hi[3];
+    uint32_t pad2_[2];
 };
 
 struct SceneDev {  // everything a traversal needs, passed by value to kernels
@@ -191,7 +195,7 @@ struct Scene {
     DevBuf<float4> result;        // per path
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
     DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
-    uint32_t t1 = 8, t2 = 8, fetch_min = 4;  // traversal thresholds (see extend_warp)
+    uint32_t t1 = 8, t2 = 8, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
     uint32_t extend_blocks_per_sm = 8;
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;

@@ -181,9 +181,11 @@ k_extend(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t 
 template <int kMinBlocks>
 __global__ void __launch_bounds__(128, kMinBlocks)
 k_extend_wide(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t n_fixed, uint32_t *fetch_ctr,
-              float4 *__restrict__ hits, int t1, int t2, int fetch_min, uint32_t magic) {
+              float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic) {
+    __shared__ uint8_t s_perm[8][256];
+    fill_perm_table(s_perm);
     const uint32_t n = n_ptr ? *n_ptr : n_fixed;
-    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, fetch_min, magic);
+    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm);
 }
 
 // ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
@@ -435,11 +437,13 @@ static int launch_extend(Scene *s, const SceneDev &sd, const ExtendIn &in, const
     RT_CUDA(ctx, prof_mark(s, st));
     if (s->wide) {
         if (s->extend_blocks_per_sm >= 8)
-            k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
+        else if (s->extend_blocks_per_sm == 7)
+            k_extend_wide<7><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
         else if (s->extend_blocks_per_sm >= 6)
-            k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
         else
-            k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
     }
     else
         k_extend<<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min);

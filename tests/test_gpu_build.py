@@ -160,33 +160,30 @@ def check_wide_tree(gs, world):
         scale = np.array([2.0 ** (((eim >> (8 * a)) & 0xFF) - 127) for a in range(3)])
         imask = eim >> 24
         child_base, prim_base = int(wu[w, 4]), int(wu[w, 5])
-        meta = wu[w, 6:8].copy().view(np.uint8)
+        leafmask = int(wu[w, 6]) & 0xFF
+        assert int(wu[w, 6]) >> 8 == 0 and (imask & leafmask) == 0
         q = wu[w, 8:20].copy().view(np.uint8).reshape(6, 8)  # qlo_x qlo_y qlo_z qhi_x qhi_y qhi_z
-        rank = 0
+        rank = off = 0
         for k in range(8):
-            m = int(meta[k])
-            if m == 0:
-                assert not (imask >> k) & 1
-                continue
             lo = org + q[0:3, k] * scale
             hi = org + q[3:6, k] * scale
+            if not ((imask | leafmask) >> k) & 1:
+                assert np.all(q[0:3, k] == 255) and np.all(q[3:6, k] == 0), "empty slots carry an inverted box"
+                continue
             assert np.all(lo <= hi)
-            if (m & 0x18) == 0x18:
-                assert (m & 7) == k and (m >> 5) == 1 and (imask >> k) & 1
-                stack.append((child_base + rank, anc + [(lo, hi)]))
+            if (imask >> k) & 1:
+                stack.append((child_base + rank, anc + [(lo, hi)]))   # internal children contiguous in slot order
                 rank += 1
             else:
-                assert not (imask >> k) & 1
-                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
-                off = m & 31
-                for s in range(prim_base + off, prim_base + off + cnt):
-                    assert s < n_bvh
-                    seen[s] += 1
-                    plo, phi = slot_box(world, int(prim[s]))
-                    # quantised boxes are each conservative for the primitives below them (a child's own
-                    # grid may stick out of its parent's slot box by a quantum, which is harmless)
-                    for blo, bhi in anc + [(lo, hi)]:
-                        assert np.all(plo >= blo) and np.all(phi <= bhi), "a box on the path does not contain the primitive"
+                s_ = prim_base + off                                    # one primitive per leaf, contiguous in slot order
+                off += 1
+                assert s_ < n_bvh
+                seen[s_] += 1
+                plo, phi = slot_box(world, int(prim[s_]))
+                # quantised boxes are each conservative for the primitives below them (a child's own
+                # grid may stick out of its parent's slot box by a quantum, which is harmless)
+                for blo, bhi in anc + [(lo, hi)]:
+                    assert np.all(plo >= blo) and np.all(phi <= bhi), "a box on the path does not contain the primitive"
     assert np.all(seen[:n_bvh] == 1), "every BVH primitive must be in exactly one wide leaf"
     assert np.all(node_seen == 1), "every wide node must be reachable exactly once"
 
