@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--leaf-max", type=int, default=0)
     ap.add_argument("--batch-spp", type=int, default=0)
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: per-rank slice sum+resolve over peer memory in one kernel (default) or NCCL reduce to rank 0 + resolve")
     ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
     return ap.parse_args()
 
@@ -233,12 +235,18 @@ def run_ours(a):
     sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
     sc.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
     stream = torch.cuda.current_stream().cuda_stream
+    xch = mg.PeerExchange(ctx, npix, rank, world_size, dev) if (world_size > 1 and a.exchange == "peer") else None
 
     def frame(step, e2e):
         if e2e:
             d_centers.copy_(h_centers, non_blocking=True)
             d_radii.copy_(h_radii, non_blocking=True)
         sc.build(stream)
+        if xch is not None:
+            mg.render_spp_split_peer(sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream)
+            if rank == 0 and e2e:
+                h_rgba8.copy_(xch.frame, non_blocking=True)
+            return
         # per-pixel XORWOW streams continue from frame to frame as in the reference (states are initialised
         # once, src/Global/RendererTime.cu:395): frame `step` owns samples [step*spp, (step+1)*spp)
         mg.render_spp_split(sc, cam, a.width, a.height, a.spp, a.depth, a.seed, accum, frame=step, stream=stream,
@@ -304,7 +312,8 @@ def run_ours(a):
             "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "parallelism": f"spp-split x{world_size} + NCCL sum" if world_size > 1 else "single GPU",
+            "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)"
+                                                                      if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
                        "step": "LBVH rebuild + render + resolve", "primary_rays": "traced once per pixel (no jitter in the reference), counted once"},
             "e2e": {"value": ee["segs"] / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
@@ -328,6 +337,8 @@ def run_ours(a):
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line))
+    if xch is not None:
+        xch.close()
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -171,6 +171,32 @@ int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *pa
 int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *dev_color_srgb,
                uint8_t *dev_rgba8, void *stream);
 
+/* ---- multi-GPU exchange step of the samples-per-pixel split (no counterpart in the reference, which
+ *      is single-GPU: docs/technical-details.md:327; north_star names the split and the sum).
+ *      One process per GPU.  Each rank renders its block of samples into an accumulation buffer
+ *      obtained from rt_peer_alloc, publishes the 64-byte handle (any host transport; the tests and
+ *      bench.py use torch.distributed.all_gather) and maps the other ranks' buffers with rt_peer_open
+ *      (CUDA IPC: NVLink / NVSwitch peer memory on a multi-GPU box, same-device mapping when two
+ *      processes share a GPU).  rt_resolve_parts is then ONE kernel that, for the pixel range
+ *      [first_pixel, first_pixel + n_pixels), loads the n_parts partial sums straight from peer
+ *      memory, adds them in index order (fixed order => the frame is bit-reproducible and equal to
+ *      the same parts summed on one GPU), divides by the total sample count, applies the display
+ *      transform of rt_resolve and stores into dev_sum_out / dev_color_srgb / dev_rgba8 (each
+ *      float4[/uchar4] per pixel of the WHOLE frame, indexed by absolute pixel, any may be NULL and
+ *      any may itself be peer memory, e.g. rank 0's frame buffer).  With every rank resolving its own
+ *      slice this is reduce-scatter + resolve + gather in one pass over NVLink.  The caller orders
+ *      the ranks (all parts complete before the call; parts not overwritten until every rank's call
+ *      has finished), e.g. with a stream-ordered NCCL barrier.  n_parts <= RT_MAX_PARTS. */
+#define RT_MAX_PARTS 16
+#define RT_PEER_HANDLE_BYTES 64
+int rt_peer_alloc(rt_context ctx, size_t bytes, void **dev_ptr_out, unsigned char handle_out[RT_PEER_HANDLE_BYTES]);
+int rt_peer_free(rt_context ctx, void *dev_ptr);
+int rt_peer_open(rt_context ctx, const unsigned char handle[RT_PEER_HANDLE_BYTES], void **dev_ptr_out);
+int rt_peer_close(rt_context ctx, void *dev_ptr);
+int rt_resolve_parts(rt_context ctx, const float *const *dev_parts, int n_parts, size_t first_pixel,
+                     size_t n_pixels, float *dev_sum_out, float *dev_color_srgb, uint8_t *dev_rgba8,
+                     void *stream);
+
 int rt_get_stats(rt_scene scene, rt_stats *out); /* synchronises the scene's last stream */
 
 /* Debug/validation export of the built BVH (device -> host copies; synchronises).

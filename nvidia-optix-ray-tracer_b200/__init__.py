@@ -30,7 +30,10 @@ ABI_SYMBOLS = [
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
+    "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
 ]
+RT_MAX_PARTS = 16
+RT_PEER_HANDLE_BYTES = 64
 
 
 class Camera(C.Structure):
@@ -101,6 +104,11 @@ def lib() -> C.CDLL:
         L.rt_accel_build.argtypes = [vp, vp]
         L.rt_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(FrameParams), C.POINTER(Outputs), vp]
         L.rt_resolve.argtypes = [vp, vp, sz, vp, vp, vp]
+        L.rt_peer_alloc.argtypes = [vp, sz, C.POINTER(vp), C.c_char_p]
+        L.rt_peer_free.argtypes = [vp, vp]
+        L.rt_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+        L.rt_peer_close.argtypes = [vp, vp]
+        L.rt_resolve_parts.argtypes = [vp, C.POINTER(vp), C.c_int, sz, sz, vp, vp, vp, vp]
         L.rt_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.rt_accel_download.argtypes = [vp, vp, vp, vp, vp]
         L.rt_accel_download_wide.argtypes = [vp, vp, vp, vp, C.POINTER(u64)]
@@ -171,6 +179,30 @@ class Context:
 
     def resolve(self, accum_ptr, n_pixels, color_ptr=None, rgba8_ptr=None, stream=None):
         self.check(lib().rt_resolve(self._h, accum_ptr, n_pixels, color_ptr, rgba8_ptr, stream))
+
+    # ---- multi-GPU exchange step (include/rtb200.h "rt_peer_*", "rt_resolve_parts")
+    def peer_alloc(self, nbytes: int):
+        """(device pointer, 64-byte handle) of a buffer other processes can map with peer_open."""
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(RT_PEER_HANDLE_BYTES)
+        self.check(lib().rt_peer_alloc(self._h, nbytes, C.byref(ptr), handle))
+        return ptr.value, handle.raw
+
+    def peer_free(self, ptr):
+        self.check(lib().rt_peer_free(self._h, ptr))
+
+    def peer_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p()
+        self.check(lib().rt_peer_open(self._h, C.create_string_buffer(bytes(handle), RT_PEER_HANDLE_BYTES), C.byref(ptr)))
+        return ptr.value
+
+    def peer_close(self, ptr):
+        self.check(lib().rt_peer_close(self._h, ptr))
+
+    def resolve_parts(self, part_ptrs, first_pixel, n_pixels, sum_ptr=None, color_ptr=None, rgba8_ptr=None, stream=None):
+        arr = (C.c_void_p * len(part_ptrs))(*part_ptrs)
+        self.check(lib().rt_resolve_parts(self._h, arr, len(part_ptrs), first_pixel, n_pixels, sum_ptr, color_ptr,
+                                          rgba8_ptr, stream))
 
     def close(self):
         if self._h:

@@ -272,6 +272,60 @@ int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *d
     return resolve(&ctx->c, dev_accum, n_pixels, dev_color_srgb, dev_rgba8, (cudaStream_t)stream);
 }
 
+int rt_peer_alloc(rt_context ctx, size_t bytes, void **dev_ptr_out, unsigned char handle_out[RT_PEER_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_PEER_HANDLE_BYTES, "IPC handle size");
+    if (!ctx || !dev_ptr_out || !handle_out || !bytes) return RT_ERR_INVALID;
+    DeviceGuard g(ctx->c.device);
+    void *p = nullptr;
+    RT_CUDA(&ctx->c, cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return rtb::set_error(&ctx->c, RT_ERR_CUDA, "cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+    }
+    memcpy(handle_out, &h, sizeof(h));
+    *dev_ptr_out = p;
+    return RT_OK;
+}
+
+int rt_peer_free(rt_context ctx, void *dev_ptr) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!dev_ptr) return RT_OK;
+    DeviceGuard g(ctx->c.device);
+    RT_CUDA(&ctx->c, cudaFree(dev_ptr));
+    return RT_OK;
+}
+
+int rt_peer_open(rt_context ctx, const unsigned char handle[RT_PEER_HANDLE_BYTES], void **dev_ptr_out) {
+    if (!ctx || !handle || !dev_ptr_out) return RT_ERR_INVALID;
+    DeviceGuard g(ctx->c.device);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *p = nullptr;
+    RT_CUDA(&ctx->c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *dev_ptr_out = p;
+    return RT_OK;
+}
+
+int rt_peer_close(rt_context ctx, void *dev_ptr) {
+    if (!ctx) return RT_ERR_INVALID;
+    if (!dev_ptr) return RT_OK;
+    DeviceGuard g(ctx->c.device);
+    RT_CUDA(&ctx->c, cudaIpcCloseMemHandle(dev_ptr));
+    return RT_OK;
+}
+
+int rt_resolve_parts(rt_context ctx, const float *const *dev_parts, int n_parts, size_t first_pixel, size_t n_pixels,
+                     float *dev_sum_out, float *dev_color_srgb, uint8_t *dev_rgba8, void *stream) {
+    if (!ctx || !dev_parts || n_parts < 1 || n_parts > RT_MAX_PARTS) return RT_ERR_INVALID;
+    for (int j = 0; j < n_parts; j++)
+        if (!dev_parts[j]) return RT_ERR_INVALID;
+    DeviceGuard g(ctx->c.device);
+    return resolve_parts(&ctx->c, dev_parts, n_parts, first_pixel, n_pixels, dev_sum_out, dev_color_srgb, dev_rgba8,
+                         (cudaStream_t)stream);
+}
+
 int rt_trace_rays(rt_scene scene, const float *dev_rays, const uint32_t *dev_skip, size_t n, float *dev_t, uint32_t *dev_id, void *stream) {
     if (!scene || (n && (!dev_rays || !dev_t || !dev_id))) return RT_ERR_INVALID;
     DeviceGuard g(scene->s.ctx->device);

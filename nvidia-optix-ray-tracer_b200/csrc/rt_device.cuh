@@ -578,18 +578,29 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
             const uint32_t m3 = __ballot_sync(FULL, alive && huge_wait);
             if (m3 && (__popc(m3) >= t3 ||
                        !__any_sync(FULL, alive && !huge_wait && ((gmask >> 8) != 0 || sp > 0 || (pmask >> 16) != 0)))) {
+                // warp-cooperative cull: the waiting rays take turns, lane k tests outlier box k
+                uint32_t mine = 0;
+                float hl0 = 0, hl1 = 0, hl2 = 0, hh0 = 0, hh1 = 0, hh2 = 0;
+                if (lane < n_huge) {
+                    hl0 = info->huge_lo[lane][0]; hl1 = info->huge_lo[lane][1]; hl2 = info->huge_lo[lane][2];
+                    hh0 = info->huge_hi[lane][0]; hh1 = info->huge_hi[lane][1]; hh2 = info->huge_hi[lane][2];
+                }
+                for (uint32_t rem = m3; rem; rem &= rem - 1u) {
+                    const int src = __ffs(rem) - 1;
+                    const float rix = __shfl_sync(FULL, ix, src), riy = __shfl_sync(FULL, iy, src), riz = __shfl_sync(FULL, iz, src);
+                    const float rox = __shfl_sync(FULL, ox, src), roy = __shfl_sync(FULL, oy, src), roz = __shfl_sync(FULL, oz, src);
+                    const float rt0 = __shfl_sync(FULL, tmin, src), rt1 = __shfl_sync(FULL, best.t, src);
+                    const float x0 = __fmaf_rn(hl0, rix, rox), x1 = __fmaf_rn(hh0, rix, rox);
+                    const float y0 = __fmaf_rn(hl1, riy, roy), y1 = __fmaf_rn(hh1, riy, roy);
+                    const float z0 = __fmaf_rn(hl2, riz, roz), z1 = __fmaf_rn(hh2, riz, roz);
+                    const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), rt0));
+                    const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), rt1));
+                    const uint32_t mm = __ballot_sync(FULL, lane < n_huge && tlo <= thi * 1.000002f);
+                    if ((int)lane == src) mine = mm;
+                }
                 if (alive && huge_wait) {
-                    uint32_t m = 0;
-                    for (uint32_t k = 0; k < n_huge; k++) {
-                        const float x0 = __fmaf_rn(info->huge_lo[k][0], ix, ox), x1 = __fmaf_rn(info->huge_hi[k][0], ix, ox);
-                        const float y0 = __fmaf_rn(info->huge_lo[k][1], iy, oy), y1 = __fmaf_rn(info->huge_hi[k][1], iy, oy);
-                        const float z0 = __fmaf_rn(info->huge_lo[k][2], iz, oz), z1 = __fmaf_rn(info->huge_hi[k][2], iz, oz);
-                        const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                        const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), best.t));
-                        if (tlo <= thi * 1.000002f) m |= 1u << k;
-                    }
                     pbase = info->huge_slot[0];
-                    pmask = 0xFFFFu | (m << 16);  // all kMaxHuge <= 16 slots present: primitive k = pbase + k
+                    pmask = 0xFFFFu | (mine << 16);  // all kMaxHuge <= 16 slots present: primitive k = pbase + k
                     huge_wait = false;
                     huge_done = true;
                 }

@@ -195,8 +195,8 @@ struct Scene {
     DevBuf<float4> result;        // per path
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
     DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
-    uint32_t t1 = 8, t2 = 8, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
-    uint32_t extend_blocks_per_sm = 8;
+    uint32_t t1 = 16, t2 = 4, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
+    uint32_t extend_blocks_per_sm = 7;
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;
 
@@ -225,6 +225,8 @@ int build_accel(Scene *s, cudaStream_t stream);
 int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *p, const rt_outputs *out,
                  cudaStream_t stream);
 int resolve(Context *ctx, const float *accum, size_t n, float *color, uint8_t *rgba8, cudaStream_t stream);
+int resolve_parts(Context *ctx, const float *const *parts, int n_parts, size_t first, size_t n, float *sum_out, float *color,
+                  uint8_t *rgba8, cudaStream_t stream);
 int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id,
                cudaStream_t stream);
 SceneDev scene_dev(const Scene *s);

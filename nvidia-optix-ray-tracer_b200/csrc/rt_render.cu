@@ -170,6 +170,53 @@ __device__ __forceinline__ void queue_write(const Queue &q, uint32_t i, F3 o, F3
     q.r4[i] = r.v4;
 }
 
+// Block-wide binned append: the rays a block emits in one step are written to the queue grouped by the
+// octant of their direction, so that the 32 lanes of a traversal warp mostly share one child-visiting
+// order (extend_warp_wide walks children in slot ^ octant order) while staying close in origin (one
+// block = a few neighbouring pixel tiles).  Results do not depend on queue order (closest hit is
+// order-free, radiance is written by path id), so this is a pure scheduling choice.
+// Must be called by every thread of the block; NW = warps per block.
+constexpr uint32_t kBins = 8;
+__device__ __forceinline__ uint32_t dir_octant(F3 d) {
+    return (d.x >= 0.0f ? 1u : 0u) | (d.y >= 0.0f ? 2u : 0u) | (d.z >= 0.0f ? 4u : 0u);
+}
+template <int NW>
+__device__ __forceinline__ uint32_t binned_push(uint32_t *counter, bool emit, uint32_t bin, uint32_t (*s_cnt)[kBins + 1],
+                                                uint32_t *s_base) {
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t key = emit ? bin : kBins;
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, key);
+    if (lane <= kBins) s_cnt[w][lane] = 0;
+    __syncwarp();
+    if ((int)lane == __ffs(peers) - 1) s_cnt[w][key] = __popc(peers);
+    __syncthreads();
+    if (w == 0) {
+        uint32_t tot = 0;
+        if (lane < kBins) {
+#pragma unroll
+            for (int ww = 0; ww < NW; ww++) {
+                const uint32_t c = s_cnt[ww][lane];
+                s_cnt[ww][lane] = tot;
+                tot += c;
+            }
+        }
+        uint32_t inc = tot;
+#pragma unroll
+        for (int o = 1; o < (int)kBins; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        uint32_t base = 0;
+        if (lane == kBins - 1 && inc) base = atomicAdd(counter, inc);
+        base = __shfl_sync(0xFFFFFFFFu, base, kBins - 1);
+        if (lane < kBins) s_base[lane] = base + inc - tot;
+    }
+    __syncthreads();
+    const uint32_t pos = emit ? s_base[key] + s_cnt[w][key] + __popc(peers & ((1u << lane) - 1u)) : 0u;
+    __syncthreads();  // s_cnt / s_base are reused by the next step
+    return pos;
+}
+
 // ------------------------------------------------------------------ closest hit for a ray buffer (persistent warps)
 __global__ void __launch_bounds__(128, 8)
 k_extend(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t n_fixed, uint32_t *fetch_ctr,
@@ -233,10 +280,13 @@ k_primary_aov(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, const float4 *__r
 // ------------------------------------------------------------------ first bounce for S samples of every pixel
 // The reference has no sub-pixel jitter (Shader.cu:249-252), so all samples of a pixel share the
 // primary hit; each sample continues with its own XORWOW stream(p, s).
-__global__ void __launch_bounds__(128)
+constexpr int kPrimaryThreads = 512;
+__global__ void __launch_bounds__(kPrimaryThreads)
 k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
                 const float4 *__restrict__ phit, uint32_t *__restrict__ rng, Queue out, uint32_t *out_count,
                 float4 *__restrict__ result) {
+    __shared__ uint32_t s_cnt[kPrimaryThreads / 32][kBins + 1];
+    __shared__ uint32_t s_base[kBins];
     uint32_t x, y;
     const bool valid = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y);
     const uint32_t npix = W * H;
@@ -266,7 +316,7 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
         Scatter sc1;
         Rng r = st;
         if (go) sc1 = scatter(sc, ray, hit, r);
-        const uint32_t qi = queue_push(out_count, go);
+        const uint32_t qi = binned_push<kPrimaryThreads / 32>(out_count, go, go ? dir_octant(sc1.dir) : 0u, s_cnt, s_base);
         if (go) {
             queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, hit.slot, r);
         } else if (valid) {
@@ -291,13 +341,16 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
 // ------------------------------------------------------------------ closest-hit / miss programs over the ray queue
 // One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
 // state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
-__global__ void __launch_bounds__(256)
+constexpr int kShadeThreads = 512;
+__global__ void __launch_bounds__(kShadeThreads)
 k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
         uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg) {
+    __shared__ uint32_t s_cnt[kShadeThreads / 32][kBins + 1];
+    __shared__ uint32_t s_base[kBins];
     const uint32_t n = *in_count;
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t w0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; w0 < n; w0 += stride) {
-        const uint32_t i = w0 + (threadIdx.x & 31u);
+    for (uint32_t b0 = blockIdx.x * blockDim.x; b0 < n; b0 += stride) {  // block-uniform trip count
+        const uint32_t i = b0 + threadIdx.x;
         const bool valid = i < n;
         bool emit = false;
         Scatter s;
@@ -333,7 +386,7 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
                 emit = true;
             }
         }
-        const uint32_t qi = queue_push(out_count, emit);
+        const uint32_t qi = binned_push<kShadeThreads / 32>(out_count, emit, emit ? dir_octant(s.dir) : 0u, s_cnt, s_base);
         if (emit) queue_write(out, qi, s.P, s.dir, thr, pid, slot, r);
     }
 }
@@ -539,19 +592,19 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             }
             RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
         }
-        const uint32_t shade_grid = (uint32_t)ctx->sm_count * 8u;
+        const uint32_t shade_grid = (uint32_t)ctx->sm_count * 4u;
         uint32_t done = 0;
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p);
+            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
                 const Queue qin = make_queue(s, d & 1), qout = make_queue(s, (d + 1) & 1);
                 const ExtendIn in{qin.o, qin.d, nullptr};
                 const int rc = launch_extend(s, sd, in, cnt + d, 0, fetch++, s->hit.p, st);
                 if (rc) return rc;
-                k_shade<<<shade_grid, 256, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg);
+                k_shade<<<shade_grid, kShadeThreads, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg);
                 s->launches += 1;
             }
             const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
@@ -576,6 +629,53 @@ int resolve(Context *ctx, const float *accum, size_t n, float *color, uint8_t *r
     if (!n) return RT_OK;
     k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(accum), n,
                                                          reinterpret_cast<float4 *>(color), reinterpret_cast<uchar4 *>(rgba8));
+    RT_CUDA(ctx, cudaGetLastError());
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------ multi-GPU: sum of peer partial sums + resolve
+// One pass over [first, first + n): 128-bit loads from up to RT_MAX_PARTS accumulation buffers (local
+// HBM or peer memory over NVLink), fixed-order sum, display transform, stores to (possibly peer) outputs.
+struct PartPtrs {
+    const float4 *p[RT_MAX_PARTS];
+};
+__global__ void __launch_bounds__(256)
+k_resolve_parts(PartPtrs parts, int n_parts, size_t first, size_t n, float4 *__restrict__ sum_out,
+                float4 *__restrict__ color, uchar4 *__restrict__ rgba8) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        const size_t p = first + k;
+        float4 v[RT_MAX_PARTS];
+#pragma unroll
+        for (int j = 0; j < RT_MAX_PARTS; j++)
+            if (j < n_parts) v[j] = __ldcg(parts.p[j] + p);  // all loads in flight before the first add
+        float4 a = v[0];
+#pragma unroll
+        for (int j = 1; j < RT_MAX_PARTS; j++)
+            if (j < n_parts) {
+                a.x += v[j].x; a.y += v[j].y; a.z += v[j].z; a.w += v[j].w;
+            }
+        if (sum_out) sum_out[p] = a;
+        if (color || rgba8) {
+            const float inv = a.w > 0.0f ? 1.0f / a.w : 0.0f;
+            const float sx = srgb(a.x * inv), sy = srgb(a.y * inv), sz = srgb(a.z * inv);
+            if (color) color[p] = make_float4(sx, sy, sz, 1.0f);
+            if (rgba8)
+                rgba8[p] = make_uchar4((unsigned char)min((unsigned int)(sx * 256.0f), 255u),
+                                       (unsigned char)min((unsigned int)(sy * 256.0f), 255u),
+                                       (unsigned char)min((unsigned int)(sz * 256.0f), 255u), 255);
+        }
+    }
+}
+
+int resolve_parts(Context *ctx, const float *const *parts, int n_parts, size_t first, size_t n, float *sum_out, float *color,
+                  uint8_t *rgba8, cudaStream_t st) {
+    if (!n) return RT_OK;
+    PartPtrs pp;
+    for (int j = 0; j < RT_MAX_PARTS; j++) pp.p[j] = reinterpret_cast<const float4 *>(parts[j < n_parts ? j : 0]);
+    const unsigned grid = (unsigned)std::min<size_t>((n + 255) / 256, (size_t)ctx->sm_count * 16);
+    k_resolve_parts<<<grid, 256, 0, st>>>(pp, n_parts, first, n, reinterpret_cast<float4 *>(sum_out),
+                                          reinterpret_cast<float4 *>(color), reinterpret_cast<uchar4 *>(rgba8));
     RT_CUDA(ctx, cudaGetLastError());
     return RT_OK;
 }

@@ -75,3 +75,105 @@ def render_spp_split(scene, cam, width, height, spp, max_depth, seed, accum, *, 
         accum.zero_()
     reduce_accum(accum, dst)
     return cnt
+
+
+# ---------------------------------------------------------------------------------------------------
+# Exchange step over peer memory (include/rtb200.h rt_peer_* / rt_resolve_parts): instead of an NCCL
+# reduce of the whole accumulation buffer to one rank followed by a resolve there, every rank sums ITS
+# slice of the pixels straight out of all ranks' accumulation buffers (mapped with CUDA IPC, i.e. NVLink
+# loads on a multi-GPU box), resolves it and stores the RGBA8 pixels into the destination rank's frame
+# buffer: reduce-scatter + resolve + gather in one kernel per rank, parts added in rank order.
+
+def pixel_slice(n_pixels: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous pixel range [first, first+count) that `rank` sums and resolves."""
+    if n_pixels < 0 or world < 1 or not (0 <= rank < world):
+        raise ValueError(f"bad slice request n_pixels={n_pixels} world={world} rank={rank}")
+    base, extra = divmod(n_pixels, world)
+    return rank * base + min(rank, extra), base + (1 if rank < extra else 0)
+
+
+class _DevMem:
+    """Minimal __cuda_array_interface__ carrier so torch can view memory the C ABI allocated."""
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def tensor_view(ptr: int, shape, dtype: str, device):
+    import torch
+    return torch.as_tensor(_DevMem(ptr, shape, {"float32": "<f4", "uint8": "|u1"}[dtype]), device=device)
+
+
+class PeerExchange:
+    """The per-rank accumulation buffers (float4 per pixel) and frame buffers (RGBA8) of all ranks,
+    mapped into this process.  Handles travel through torch.distributed (any backend)."""
+
+    def __init__(self, ctx, n_pixels: int, rank: int, world: int, device):
+        import torch
+        import torch.distributed as dist
+        self.ctx, self.n_pixels, self.rank, self.world, self.device = ctx, n_pixels, rank, world, device
+        self.accum_ptr, h_acc = ctx.peer_alloc(n_pixels * 16)
+        self.frame_ptr, h_frm = ctx.peer_alloc(n_pixels * 4)
+        self.accum = tensor_view(self.accum_ptr, (n_pixels, 4), "float32", device)
+        self.frame = tensor_view(self.frame_ptr, (n_pixels, 4), "uint8", device)
+        self.accum.zero_()
+        self.frame.zero_()
+        mine = torch.frombuffer(bytearray(h_acc + h_frm), dtype=torch.uint8)
+        nccl = dist.get_backend() == "nccl"
+        if nccl:
+            mine = mine.to(device)
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        self.parts, self.frames, self._opened = [], [], []
+        for r in range(world):
+            if r == rank:
+                self.parts.append(self.accum_ptr)
+                self.frames.append(self.frame_ptr)
+                continue
+            hb = bytes(allh[r].cpu().numpy().tobytes())
+            a, f = ctx.peer_open(hb[:64]), ctx.peer_open(hb[64:])
+            self.parts.append(a)
+            self.frames.append(f)
+            self._opened += [a, f]
+        self._token = torch.zeros(1, device=device if nccl else "cpu")
+        self._nccl = nccl
+
+    def fence(self):
+        """Every rank's work enqueued so far is complete before anything enqueued after this runs
+        (NCCL: a stream-ordered 4-byte all-reduce; other backends: device sync + host barrier)."""
+        import torch
+        import torch.distributed as dist
+        if self._nccl:
+            dist.all_reduce(self._token)
+        else:
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def resolve_slice(self, dst: int = 0, stream=None, sum_out_ptr=None):
+        """Sum + resolve this rank's pixel slice from all ranks' partial sums into rank `dst`'s frame."""
+        first, cnt = pixel_slice(self.n_pixels, self.world, self.rank)
+        self.fence()
+        self.ctx.resolve_parts(self.parts, first, cnt, sum_out_ptr, None, self.frames[dst], stream)
+        self.fence()
+
+    def close(self):
+        import torch
+        torch.cuda.synchronize()
+        for p in self._opened:
+            self.ctx.peer_close(p)
+        self._opened = []
+        self.accum = self.frame = None
+        self.ctx.peer_free(self.accum_ptr)
+        self.ctx.peer_free(self.frame_ptr)
+
+
+def render_spp_split_peer(scene, xch: PeerExchange, cam, width, height, spp, max_depth, seed, *, frame: int = 0,
+                          background=(0.7, 0.8, 0.9), stream=None, dst: int = 0):
+    """One frame of the spp split with the peer-memory exchange: this rank's sample block goes into its
+    own exchange buffer, then every rank sums and resolves its pixel slice into rank `dst`'s RGBA8 frame."""
+    off, cnt = frame_sample_offset(frame, spp, xch.world, xch.rank)
+    if cnt:
+        scene.render(cam, width, height, cnt, max_depth, seed, background, off, 0, xch.accum_ptr, None, None, None, stream)
+    else:
+        xch.accum.zero_()
+    xch.resolve_slice(dst, stream)
+    return cnt

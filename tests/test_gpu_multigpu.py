@@ -75,3 +75,78 @@ def test_two_rank_spp_split_matches_single_rank(tmp_path, pkg, synth):
         assert np.array_equal(got[:, 3], full[:, 3])
         assert np.abs(got[:, :3] - full[:, :3]).max() < 4e-6   # fp32 re-association of two partial sums
     gs.close()
+
+
+# ---------------------------------------------------------------------------------------------------
+# Peer-memory exchange (rt_peer_* + rt_resolve_parts): two processes map each other's accumulation
+# buffers (NVLink peers on a multi-GPU box, CUDA IPC on the shared GPU otherwise); each sums and
+# resolves its pixel slice into rank 0's RGBA8 frame.  Fixed part order => bit-exact against the same
+# two partial sums added on the host and resolved by the reference's colour functions (oracle).
+def _peer_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world),
+                      LOCAL_RANK=str(rank))
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, HERE)
+    import torch
+    import torch.distributed as dist
+    import scenes
+    pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
+    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
+    mg = importlib.import_module("nvidia-optix-ray-tracer_b200.multigpu")
+    ngpu = torch.cuda.device_count()
+    nccl = ngpu >= world
+    dev = rank if nccl else 0
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl" if nccl else "gloo", rank=rank, world_size=world)
+    gs = scenes.GpuScene(pkg, _scene(pkg, synth), device=f"cuda:{dev}")
+    cam = pkg.camera_configure([2.2, 0.1, 0.2], [0, 0, 0], [0, 0, 1], False)
+    xch = mg.PeerExchange(gs.ctx, W * H, rank, world, f"cuda:{dev}")
+    stream = torch.cuda.current_stream().cuda_stream
+    for frame in range(2):
+        mg.render_spp_split_peer(gs.scene, xch, cam, W, H, SPP, DEPTH, SEED, frame=frame, stream=stream)
+        torch.cuda.synchronize()
+        np.save(os.path.join(out_dir, f"part_{frame}_{rank}.npy"), xch.accum.cpu().numpy())
+        if rank == 0:
+            np.save(os.path.join(out_dir, f"frame_{frame}.npy"), xch.frame.cpu().numpy())
+        xch.fence()  # nobody starts the next frame before the copies above are done
+    xch.close()
+    gs.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_peer_exchange_is_bit_exact(tmp_path, pkg, synth):
+    import torch
+    import torch.multiprocessing as mp
+    import oracle_lib
+    import scenes
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_peer_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    orc = oracle_lib.load()
+    gs = scenes.GpuScene(pkg, _scene(pkg, synth))
+    cam = pkg.camera_configure([2.2, 0.1, 0.2], [0, 0, 0], [0, 0, 1], False)
+    mg = importlib.import_module("nvidia-optix-ray-tracer_b200.multigpu")
+    for frame in range(2):
+        parts = [np.load(tmp_path / f"part_{frame}_{r}.npy") for r in range(2)]
+        # each rank's partial sum is exactly what one GPU renders for that sample block
+        for r in range(2):
+            off, cnt = mg.frame_sample_offset(frame, SPP, 2, r)
+            solo = gs.render(cam, W, H, cnt, DEPTH, SEED, sample_offset=off, want=("accum",))["accum"]
+            assert np.array_equal(parts[r].view(np.uint32), solo.view(np.uint32))
+        total = (parts[0] + parts[1]).astype(np.float32)  # the kernel's order: part 0 + part 1
+        got = np.load(tmp_path / f"frame_{frame}.npy")
+        # (a) bit-exact against the single-GPU resolve kernel applied to the host-side sum
+        t = torch.from_numpy(total).cuda()
+        u8 = torch.zeros((W * H, 4), dtype=torch.uint8, device="cuda")
+        gs.ctx.resolve(t.data_ptr(), W * H, None, u8.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert np.array_equal(got, u8.cpu().numpy())
+        # (b) within one code value of the reference's colorToUchar4 (CUDA powf vs glibc powf differ by <= 2 ulp)
+        idx = np.random.default_rng(frame).integers(0, W * H, 200)
+        inv = np.float32(1.0) / total[idx, 3]
+        wu = np.array([orc.color_to_uchar4(total[i, :3] * k) for i, k in zip(idx, inv)])
+        assert np.abs(got[idx].astype(int) - wu.astype(int)).max() <= 1
+    gs.close()

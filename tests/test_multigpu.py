@@ -103,3 +103,17 @@ def test_gloo_world2_spp_split_and_frame_parallel(tmp_path, pkg, synth, oracle, 
         want = oracle.render(wd, cam, 48, 32, 2, 5, 100 + f)["accum"]
         got = np.load(tmp_path / f"frame_{f}.npy")
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32))   # byte-identical to the serial run
+
+
+def test_pixel_slices_tile_the_frame():
+    mg = _mg()
+    for n in (0, 1, 7, 1920 * 1080, 3840 * 2160 + 3):
+        for world in (1, 2, 3, 8):
+            pos = 0
+            for r in range(world):
+                first, cnt = mg.pixel_slice(n, world, r)
+                assert first == pos and cnt >= 0
+                pos += cnt
+            assert pos == n
+    with pytest.raises(ValueError):
+        mg.pixel_slice(10, 2, 2)
