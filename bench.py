@@ -41,10 +41,13 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n-spheres", type=int, default=10_000_000)
+    ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
+                    help="c4: 10M uniform spheres, 4K/64spp, spp split (headline); c5: 100M-sphere DEM packing time series, "
+                         "per-frame advect + LBVH rebuild + 16 spp, frame-parallel")
+    ap.add_argument("--n-spheres", type=int, default=0, help="0 = the workload's size (c4 10M, c5 100M)")
     ap.add_argument("--width", type=int, default=3840)
     ap.add_argument("--height", type=int, default=2160)
-    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--spp", type=int, default=0, help="0 = the workload's spp (c4 64, c5 16)")
     ap.add_argument("--depth", type=int, default=5)
     ap.add_argument("--radius", type=float, default=1.3e-3)
     ap.add_argument("--seed", type=int, default=1)
@@ -55,7 +58,12 @@ def parse():
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: per-rank slice sum+resolve over peer memory in one kernel (default) or NCCL reduce to rank 0 + resolve")
     ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if not a.n_spheres:
+        a.n_spheres = 10_000_000 if a.workload == "c4" else 100_000_000
+    if not a.spp:
+        a.spp = 64 if a.workload == "c4" else 16
+    return a
 
 
 def workload_name(a):
@@ -346,9 +354,155 @@ def run_ours(a):
     ctx.close()
 
 
+# ---------------------------------------------------------------------------------------------------
+def run_c5(a):
+    """BASELINE config 5: DEM packing time series, frame-parallel.  One step = every rank takes the next
+    frame of the series (frame = step * world + rank): device-side particle update (rt_spheres_advect, the
+    reference's Mesh-mode translation) -> full LBVH rebuild -> spp samples at 4K -> resolve.  No data-path
+    collective; `value` = segments of all ranks / max-over-ranks time."""
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
+    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
+    mg = importlib.import_module("nvidia-optix-ray-tracer_b200.multigpu")
+    rank, local, world_size = mg.env_world()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world_size == a.gpus or world_size == 1 and a.gpus == 1, f"launch with torchrun --nproc-per-node {a.gpus}"
+    dt, frames_total = 0.01, 256
+
+    centers, radii = synth.hcp_spheres_chunked(a.n_spheres)
+    n = len(radii)
+    vel = synth.dem_velocities(n)
+    ramp = pkg.bake_color_ramp("terrain", n).astype(np.float32)
+    npix = a.width * a.height
+    h_c, h_r, h_v = (torch.from_numpy(x).pin_memory() for x in (centers, radii, vel))
+    d_base_c, d_base_r, d_vel = h_c.to(dev), h_r.to(dev), h_v.to(dev)
+    d_c, d_r = torch.empty_like(d_base_c), torch.empty_like(d_base_r)
+    accum = torch.zeros((npix, 4), dtype=torch.float32, device=dev)
+    rgba8 = torch.zeros((npix, 4), dtype=torch.uint8, device=dev)
+    h_rgba8 = torch.zeros((npix, 4), dtype=torch.uint8).pin_memory()
+
+    ctx = pkg.Context(local)
+    sc = pkg.Scene(ctx)
+    for kv in a.opt:
+        k, v = kv.split("=")
+        sc.set_option(k, int(v))
+    sc.set_option("profile", 1)
+    metals = np.float32([[0.8, 0.85, 0.88, 0.0]])
+    sc.set_materials(ramp.ctypes.data, n, metals.ctypes.data, 1)
+    g_s = sc.add_spheres(d_c.data_ptr(), d_r.data_ptr(), n)
+    sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 0, 1)   # one terrain-ramp colour per particle
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def frame(step, e2e):
+        f = (step * world_size + rank) % frames_total
+        if e2e:  # the frame's particle file arrives from the host: positions, radii, velocities
+            d_base_c.copy_(h_c, non_blocking=True)
+            d_base_r.copy_(h_r, non_blocking=True)
+            d_vel.copy_(h_v, non_blocking=True)
+        # position(f) = base + velocity * (dt * frames_total) / frames_total * f   (RendererMesh.cu:383-388)
+        ctx.spheres_advect(d_base_c.data_ptr(), d_base_r.data_ptr(), d_vel.data_ptr(), n, dt * frames_total, frames_total, f,
+                           [0.0, 0.0, 0.0], [1.0, 1.0, 1.0], d_c.data_ptr(), d_r.data_ptr(), stream)
+        sc.build(stream)
+        cam = pkg.camera_configure(**synth.c5_camera(f, dt))
+        sc.render(cam, a.width, a.height, a.spp, a.depth, a.seed, (0.7, 0.8, 0.9), f * a.spp, 0, accum.data_ptr(), None, None,
+                  None, stream)
+        ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
+        if e2e:
+            h_rgba8.copy_(rgba8, non_blocking=True)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e, sampler=None):
+        for i in range(a.warmup):
+            frame(i, e2e)
+        barrier()
+        st0 = sc.stats()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps):
+            frame(a.warmup + i, e2e)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        st1 = sc.stats()
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        sg = torch.tensor([float(st1.segments_total - st0.segments_total)], device=dev, dtype=torch.float64)
+        if world_size > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(sg, op=dist.ReduceOp.SUM)
+        return dict(ms=float(t.item()), segs=float(sg.item()), trace_ms=float(st1.trace_ms), build_ms=float(st1.build_ms),
+                    launches=int(st1.kernel_launches - st0.kernel_launches), st=st1)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    dv = timed(False, sampler)
+    clocks = sampler.stop() if sampler else None
+    ee = timed(True)
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        st = dv["st"]
+        n_prims = int(st.n_prims)
+        bseg = seg_bytes(n_prims)
+        seg_step = dv["segs"] / world_size / a.steps
+        trace_step = dv["trace_ms"] / a.steps
+        n_launch = max(1, int(st.trace_launches))
+        achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
+        line = {
+            "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C5 synthetic {n} sphere jittered-HCP DEM packing (phi 0.55), 256-frame series dt=0.01, "
+                                   f"{a.width}x{a.height}, {a.spp} spp, depth {a.depth}",
+                       "parallelism": f"frame-parallel x{world_size} (frame = step*{world_size}+rank), no data-path collective",
+                       "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
+                       "step": "per rank: advect particles (device) + LBVH rebuild + render + resolve of one frame",
+                       "primary_rays": "traced once per pixel (no jitter in the reference), counted once"},
+            "e2e": {"value": ee["segs"] / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
+                    "h2d_bytes_per_step": int(4 * (h_c.numel() + h_r.numel() + h_v.numel())) * world_size,
+                    "d2h_bytes_per_step": int(h_rgba8.numel()) * world_size},
+            "gpu_launches": dv["launches"] * world_size,
+            "clocks": clocks,
+            "frames_per_s": world_size * a.steps / (dv["ms"] * 1e-3),
+            "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
+                      "n_prims": n_prims, "bytes_per_prim": 224,
+                      "hbm_frac": (n_prims * 224 / (dv["build_ms"] * 1e-3) / 1e9 / peak) if dv["build_ms"] > 0 else None},
+            "roofline": {"bound": "hbm", "kernel": "k_extend_wide (BVH traversal)", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "bytes_per_segment": bseg, "segments_per_launch": seg_step * a.steps / n_launch,
+                         "avg_launch_ms": dv["trace_ms"] / n_launch, "trace_ms_per_step": trace_step,
+                         "trace_share_of_step": trace_step / (dv["ms"] / a.steps)},
+            "segments_per_step": seg_step,
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line))
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sc.close()
+    ctx.close()
+
+
 if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "c5":
+        run_c5(args)
     else:
         run_ours(args)

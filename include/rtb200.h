@@ -160,6 +160,20 @@ int rt_scene_set_transforms(rt_scene scene, const float *transforms, size_t firs
  * hierarchy, bottom-up refit).  Called once per frame. */
 int rt_accel_build(rt_scene scene, void *stream);
 
+/* ---- per-frame particle update on the device: the translation-only transform loop of Mesh mode
+ *      (src/Global/RendererMesh.cu:378-391: shift = particleOffset + (velocity * duration / frames) * frame,
+ *      constructTransformMatrix(shift, 0, particleScale)) applied to sphere particles in place of the
+ *      reference's O(n) host loop + H2D copy of OptixInstance[] (RendererMesh.cu:393-399).  For
+ *      particle i:  center_out = particle_scale * base_center + shift_i,  radius_out = particle_scale[0]
+ *      * base_radius (uniform scale required for spheres).  Same operation order as rt_transform_mesh
+ *      followed by the instance flattening of rt_accel_build, so the results are bit-identical to the
+ *      host path.  All pointers are device pointers (float3 / float per particle); outputs may alias
+ *      nothing else.  Feed the outputs to rt_scene_add_spheres / rt_scene_update_group. */
+int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float *dev_base_radii,
+                      const float *dev_velocities, size_t n, float duration, size_t frames_this_file,
+                      size_t frame, const float particle_shift[3], const float particle_scale[3],
+                      float *dev_centers_out, float *dev_radii_out, void *stream);
+
 /* ---- launch: replaces optixLaunch(pipeline, stream, params, sbt, w, h, 1) and the raygen /
  *      closest-hit / miss programs of shader/Shader.cu ---------------------------------------- */
 int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *params,

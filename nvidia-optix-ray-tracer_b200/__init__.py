@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
-    "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
+    "rt_spheres_advect", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
 ]
 RT_MAX_PARTS = 16
 RT_PEER_HANDLE_BYTES = 64
@@ -104,6 +104,7 @@ def lib() -> C.CDLL:
         L.rt_accel_build.argtypes = [vp, vp]
         L.rt_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(FrameParams), C.POINTER(Outputs), vp]
         L.rt_resolve.argtypes = [vp, vp, sz, vp, vp, vp]
+        L.rt_spheres_advect.argtypes = [vp, vp, vp, vp, sz, C.c_float, sz, sz, f_p, f_p, vp, vp, vp]
         L.rt_peer_alloc.argtypes = [vp, sz, C.POINTER(vp), C.c_char_p]
         L.rt_peer_free.argtypes = [vp, vp]
         L.rt_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
@@ -179,6 +180,11 @@ class Context:
 
     def resolve(self, accum_ptr, n_pixels, color_ptr=None, rgba8_ptr=None, stream=None):
         self.check(lib().rt_resolve(self._h, accum_ptr, n_pixels, color_ptr, rgba8_ptr, stream))
+
+    def spheres_advect(self, base_c_ptr, base_r_ptr, vel_ptr, n, duration, frames, frame, pshift, pscale, out_c_ptr, out_r_ptr,
+                       stream=None):
+        self.check(lib().rt_spheres_advect(self._h, base_c_ptr, base_r_ptr, vel_ptr, n, duration, frames, frame, _fa(pshift),
+                                           _fa(pscale), out_c_ptr, out_r_ptr, stream))
 
     # ---- multi-GPU exchange step (include/rtb200.h "rt_peer_*", "rt_resolve_parts")
     def peer_alloc(self, nbytes: int):

@@ -272,6 +272,18 @@ int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *d
     return resolve(&ctx->c, dev_accum, n_pixels, dev_color_srgb, dev_rgba8, (cudaStream_t)stream);
 }
 
+int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float *dev_base_radii, const float *dev_velocities,
+                      size_t n, float duration, size_t frames_this_file, size_t frame, const float particle_shift[3],
+                      const float particle_scale[3], float *dev_centers_out, float *dev_radii_out, void *stream) {
+    if (!ctx || !particle_shift || !particle_scale || !frames_this_file) return RT_ERR_INVALID;
+    if (n && (!dev_base_centers || !dev_base_radii || !dev_velocities || !dev_centers_out || !dev_radii_out)) return RT_ERR_INVALID;
+    if (particle_scale[0] != particle_scale[1] || particle_scale[0] != particle_scale[2])
+        return rtb::set_error(&ctx->c, RT_ERR_UNSUPPORTED, "rt_spheres_advect: non-uniform particle scale on spheres");
+    DeviceGuard g(ctx->c.device);
+    return rtb::spheres_advect(&ctx->c, dev_base_centers, dev_base_radii, dev_velocities, n, duration, frames_this_file, frame,
+                               particle_shift, particle_scale, dev_centers_out, dev_radii_out, (cudaStream_t)stream);
+}
+
 int rt_peer_alloc(rt_context ctx, size_t bytes, void **dev_ptr_out, unsigned char handle_out[RT_PEER_HANDLE_BYTES]) {
     static_assert(sizeof(cudaIpcMemHandle_t) == RT_PEER_HANDLE_BYTES, "IPC handle size");
     if (!ctx || !dev_ptr_out || !handle_out || !bytes) return RT_ERR_INVALID;

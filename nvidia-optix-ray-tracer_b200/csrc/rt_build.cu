@@ -791,6 +791,38 @@ k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict
     }
 }
 
+// ------------------------------------------------------------------ per-frame particle update (Mesh-mode translation)
+// src/Global/RendererMesh.cu:378-391 + DeviceFunctions.cuh:133-148 with zero rotation, one thread per
+// coordinate so that the float3 arrays are read and written fully coalesced (12 B per particle each way).
+__global__ void __launch_bounds__(256)
+k_spheres_advect(const float *__restrict__ base_c, const float *__restrict__ base_r, const float *__restrict__ vel, size_t n,
+                 float duration, float frames, float frame, F3 pshift, F3 pscale, float *__restrict__ out_c,
+                 float *__restrict__ out_r) {
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= 3 * n) return;
+    const uint32_t a = (uint32_t)(k % 3);
+    const float sh = a == 0 ? pshift.x : (a == 1 ? pshift.y : pshift.z);
+    const float sc = a == 0 ? pscale.x : (a == 1 ? pscale.y : pscale.z);
+    const float total = vel[k] * duration;       // RendererMesh.cu:383
+    const float per_frame = total / frames;      // :386
+    const float shift = sh + per_frame * frame;  // :388
+    out_c[k] = sc * base_c[k] + shift;           // row a of the 3x4 matrix applied to the centre
+    if (a == 0) out_r[k / 3] = base_r[k / 3] * sqrtf((pscale.x * pscale.x + 0.0f) + 0.0f);  // k_flatten's radius scale
+}
+
+int spheres_advect(Context *ctx, const float *base_c, const float *base_r, const float *vel, size_t n, float duration,
+                   size_t frames, size_t frame, const float *pshift, const float *pscale, float *out_c, float *out_r,
+                   cudaStream_t st) {
+    if (!n) return RT_OK;
+    const size_t blocks = (3 * n + 255) / 256;
+    if (blocks > 0x7FFFFFFFull) return set_error(ctx, RT_ERR_INVALID, "too many particles");
+    k_spheres_advect<<<(unsigned)blocks, 256, 0, st>>>(base_c, base_r, vel, n, duration, (float)frames, (float)frame,
+                                                      F3{pshift[0], pshift[1], pshift[2]}, F3{pscale[0], pscale[1], pscale[2]},
+                                                      out_c, out_r);
+    RT_CUDA(ctx, cudaGetLastError());
+    return RT_OK;
+}
+
 // ------------------------------------------------------------------ host driver
 static inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 

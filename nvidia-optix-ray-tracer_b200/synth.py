@@ -92,3 +92,51 @@ def box_walls(open_plus_x: bool = True):
 def c4_camera():
     """C4 camera: centre (2.2,0,0) -> target 0, up (0,0,1), OpenGL convention (no up flip)."""
     return dict(center=(2.2, 0.0, 0.0), target=(0.0, 0.0, 0.0), up=(0.0, 0.0, 1.0), flip_up=False)
+
+
+# ------------------------------------------------------------------ C5: DEM packing time series
+def hcp_spheres_chunked(n_target: int, phi: float = 0.55, jitter: float = 0.1, seed: int = 0x5EED0005,
+                        chunk_i: int = 16):
+    """Same lattice, order and jitter as hcp_spheres, generated in slabs of `chunk_i` x-layers so that
+    100M spheres need ~2 GB of host memory instead of ~15 GB.  Returns (centers f32[n,3], radii f32[n])."""
+    r = (phi * 3.0 / (4.0 * np.pi * n_target)) ** (1.0 / 3.0)
+    a = 2.0 * r * (0.74048 / phi) ** (1.0 / 3.0)
+    nx = int(np.floor((1.0 - 2 * r) / a)) + 1
+    ny = int(np.floor((1.0 - 2 * r) / (a * np.sqrt(3) / 2))) + 1
+    nz = int(np.floor((1.0 - 2 * r) / (a * np.sqrt(6) / 3))) + 1
+    out = np.empty((n_target, 3), dtype=np.float32)
+    n = 0
+    lim = 1 - 2 * r
+    for i0 in range(0, nx, chunk_i):
+        if n >= n_target:
+            break
+        i, j, k = np.meshgrid(np.arange(i0, min(nx, i0 + chunk_i)), np.arange(ny), np.arange(nz), indexing="ij")
+        i, j, k = i.ravel(), j.ravel(), k.ravel()
+        x = (i + 0.5 * ((j + k) % 2)) * a
+        y = (j + ((k % 2) / 3.0)) * (a * np.sqrt(3) / 2)
+        z = k * (a * np.sqrt(6) / 3)
+        keep = (x <= lim) & (y <= lim) & (z <= lim)
+        c = np.stack([x[keep], y[keep], z[keep]], 1)[: n_target - n]
+        m = len(c)
+        idx = np.arange(n, n + m, dtype=np.uint64) * np.uint64(3)
+        jit = np.stack([uniform01(seed, idx + np.uint64(q)) for q in range(3)], 1)
+        out[n:n + m] = (c + r - 0.5 + (jit * 2.0 - 1.0) * (jitter * r)).astype(np.float32)
+        n += m
+    return np.ascontiguousarray(out[:n]), np.full(n, r, dtype=np.float32)
+
+
+def dem_velocities(n: int, seed: int = 0x5EED00D5, chunk: int = 1 << 22):
+    """C5 analytic motion z(t) = z0 - 2 t (1 + 0.1 hash(id)) as a per-particle velocity (0, 0, vz):
+    the frame update is then the reference's Mesh-mode translation (velocity * duration / frames * frame)."""
+    v = np.zeros((n, 3), dtype=np.float32)
+    for start in range(0, n, chunk):
+        stop = min(n, start + chunk)
+        h = uniform01(seed, np.arange(start, stop, dtype=np.uint64))
+        v[start:stop, 2] = np.float32(-2.0) * (np.float32(1.0) + np.float32(0.1) * h)
+    return v
+
+
+def c5_camera(frame: int, dt: float = 0.01):
+    """Camera of C5: the C4 view, following the mean fall of the packing (-2.1 t along z)."""
+    dz = -2.1 * dt * frame
+    return dict(center=[2.2, 0.0, dz], target=[0.0, 0.0, dz], up=[0.0, 0.0, 1.0], flip_up=False)
