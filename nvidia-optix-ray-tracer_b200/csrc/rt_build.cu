@@ -230,10 +230,12 @@ __global__ void k_decide(const uint32_t *__restrict__ bucket_tab, uint32_t n_tot
         info->scene_hi[a] = 0.0f;
     }
     for (uint32_t i = 0; i < kMaxHuge; i++) info->huge_slot[i] = (n_total - n_huge) + i;
-    info->n_wnodes = 0;
+    info->n_wnodes = 1;  // the root's slot; k_collapse allocates the rest
     info->n_wprims = 0;
     info->level_end = 0;
     info->pad_ = 0;
+    info->pad2_[0] = 0;  // k_collapse's grid barrier: arrivals, generation
+    info->pad2_[1] = 0;
 }
 
 // ------------------------------------------------------------------ K3: 30-bit Morton keys
@@ -444,6 +446,8 @@ __device__ __forceinline__ int encode_child(int first, int last, int internal_id
     if (cnt <= leaf_max) return (int)(kLeafFlag | ((uint32_t)(cnt - 1) << kLeafCountShift) | (uint32_t)first);
     return internal_idx;
 }
+constexpr uint32_t kRefitBlock = 512;  // leaves per block of k_refit_local
+constexpr uint32_t kLinkParentCross = 0x80000000u, kLinkSelfCross = 0x40000000u, kLinkIndexMask = 0x0FFFFFFFu;
 __global__ void __launch_bounds__(256)
 k_hierarchy(const uint32_t *__restrict__ keys, const BuildInfo *__restrict__ info, Node *__restrict__ nodes,
             uint32_t *__restrict__ parent_int, uint32_t *__restrict__ parent_leaf, int leaf_max) {
@@ -467,8 +471,13 @@ k_hierarchy(const uint32_t *__restrict__ keys, const BuildInfo *__restrict__ inf
     const int split = i + s * d + min(d, 0);
     const int first = min(i, j), last = max(i, j);
     // topology links (always the full Karras tree: the refit climbs through collapsed nodes too)
-    if (split == first) parent_leaf[split] = ((uint32_t)i << 1) | 0u; else parent_int[split] = ((uint32_t)i << 1) | 0u;
-    if (split + 1 == last) parent_leaf[split + 1] = ((uint32_t)i << 1) | 1u; else parent_int[split + 1] = ((uint32_t)i << 1) | 1u;
+    // link = parent index << 1 | which child, plus two flags for the two-kernel refit: bit 31 = the parent's
+    // leaf range crosses a boundary of kRefitBlock consecutive leaves, bit 30 = the child's own range does
+    const uint32_t pc = ((uint32_t)first / kRefitBlock != (uint32_t)last / kRefitBlock) ? kLinkParentCross : 0u;
+    const uint32_t c0c = ((uint32_t)first / kRefitBlock != (uint32_t)split / kRefitBlock) ? kLinkSelfCross : 0u;
+    const uint32_t c1c = ((uint32_t)(split + 1) / kRefitBlock != (uint32_t)last / kRefitBlock) ? kLinkSelfCross : 0u;
+    if (split == first) parent_leaf[split] = ((uint32_t)i << 1) | 0u | pc; else parent_int[split] = ((uint32_t)i << 1) | 0u | pc | c0c;
+    if (split + 1 == last) parent_leaf[split + 1] = ((uint32_t)i << 1) | 1u | pc; else parent_int[split + 1] = ((uint32_t)i << 1) | 1u | pc | c1c;
     if (i == 0) parent_int[0] = 0xFFFFFFFFu;
     // child pointers seen by traversal: ranges of <= leaf_max prims become one leaf
     const int c0 = encode_child(first, split, split, leaf_max);
@@ -502,11 +511,96 @@ k_refit(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12
     Box3 b = pad_box(prim_box(slot_geom[i], tri_v12));
     uint32_t link = parent_leaf[i];
     while (true) {
-        const uint32_t p = link >> 1, which = link & 1u;
+        const uint32_t p = (link >> 1) & kLinkIndexMask, which = link & 1u;
         store_child_box(nodes + p, which, b);
         __threadfence();
         if (atomicAdd(visit + p, 1u) == 0u) return;  // sibling not done yet
         // second arriver: read the sibling's box (written before its fence) from L2
+        const float4 *q = reinterpret_cast<const float4 *>(nodes + p);
+        const float4 sxy = __ldcg(q + (which ^ 1u));
+        const float2 sz = __ldcg(reinterpret_cast<const float2 *>(q + 2) + (which ^ 1u));
+        b.lo = f3(fminf(b.lo.x, sxy.x), fminf(b.lo.y, sxy.z), fminf(b.lo.z, sz.x));
+        b.hi = f3(fmaxf(b.hi.x, sxy.y), fmaxf(b.hi.y, sxy.w), fmaxf(b.hi.z, sz.y));
+        link = parent_int[p];
+        if (link == 0xFFFFFFFFu) {
+            info->scene_lo[0] = b.lo.x; info->scene_lo[1] = b.lo.y; info->scene_lo[2] = b.lo.z;
+            info->scene_hi[0] = b.hi.x; info->scene_hi[1] = b.hi.y; info->scene_hi[2] = b.hi.z;
+            return;
+        }
+    }
+}
+
+// Two-kernel variant (option "refit_mode" = 1).  k_refit_local: one block per kRefitBlock consecutive
+// leaves climbs every subtree that lies inside the block, handing boxes over through shared memory
+// (shared counter + block-level fence, no global atomics, no device-wide fences) and stops at the first
+// parent whose range crosses a block boundary.  k_refit_top: the nodes that stopped there (a leaf or an
+// in-block subtree root whose parent crosses) carry on with the global counter scheme; that is ~n/50
+// starters instead of n.
+__global__ void __launch_bounds__(kRefitBlock)
+k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info, Node *nodes,
+              const uint32_t *__restrict__ parent_int, const uint32_t *__restrict__ parent_leaf) {
+    __shared__ float s_box[2][6][kRefitBlock];  // [which child][lo.xyz hi.xyz][node slot]
+    __shared__ uint32_t s_visit[kRefitBlock];
+    const uint32_t n = info->n_bvh;
+    const uint32_t b0 = blockIdx.x * kRefitBlock;
+    const uint32_t i = b0 + threadIdx.x;
+    s_visit[threadIdx.x] = 0;
+    __syncthreads();
+    if (n < 2 || i >= n) return;
+    Box3 b = pad_box(prim_box(slot_geom[i], tri_v12));
+    uint32_t link = parent_leaf[i];
+    for (;;) {
+        if (link == 0xFFFFFFFFu) {  // the whole tree sits in this block
+            info->scene_lo[0] = b.lo.x; info->scene_lo[1] = b.lo.y; info->scene_lo[2] = b.lo.z;
+            info->scene_hi[0] = b.hi.x; info->scene_hi[1] = b.hi.y; info->scene_hi[2] = b.hi.z;
+            return;
+        }
+        const uint32_t p = (link >> 1) & kLinkIndexMask, which = link & 1u;
+        store_child_box(nodes + p, which, b);
+        if (link & kLinkParentCross) return;  // k_refit_top continues from here
+        const uint32_t next = parent_int[p];  // issued before the hand-over: off the critical path
+        const uint32_t l = p - b0;            // a Karras node's index is one end of its range
+        float(*mine)[kRefitBlock] = s_box[which];
+        mine[0][l] = b.lo.x; mine[1][l] = b.lo.y; mine[2][l] = b.lo.z;
+        mine[3][l] = b.hi.x; mine[4][l] = b.hi.y; mine[5][l] = b.hi.z;
+        __threadfence_block();
+        if (atomicAdd(&s_visit[l], 1u) == 0u) return;  // the sibling will pick this box up
+        __threadfence_block();
+        volatile float(*sib)[kRefitBlock] = s_box[which ^ 1u];
+        b.lo = f3(fminf(b.lo.x, sib[0][l]), fminf(b.lo.y, sib[1][l]), fminf(b.lo.z, sib[2][l]));
+        b.hi = f3(fmaxf(b.hi.x, sib[3][l]), fmaxf(b.hi.y, sib[4][l]), fmaxf(b.hi.z, sib[5][l]));
+        link = next;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_refit_top(const float4 *__restrict__ slot_geom, const float4 *__restrict__ tri_v12, BuildInfo *info, Node *nodes,
+            const uint32_t *__restrict__ parent_int, const uint32_t *__restrict__ parent_leaf, uint32_t *visit) {
+    const uint32_t n = info->n_bvh;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < 2 || t >= 2 * n - 1) return;
+    uint32_t link;
+    Box3 b;
+    if (t < n) {
+        link = parent_leaf[t];
+        if (!(link & kLinkParentCross)) return;
+        b = pad_box(prim_box(slot_geom[t], tri_v12));
+    } else {
+        const uint32_t q = t - n;
+        link = parent_int[q];
+        if (link == 0xFFFFFFFFu || !(link & kLinkParentCross) || (link & kLinkSelfCross)) return;
+        const float4 *c = reinterpret_cast<const float4 *>(nodes + q);  // both child boxes, written by k_refit_local
+        const float4 c0 = c[0], c1 = c[1], cz = c[2];
+        b.lo = f3(fminf(c0.x, c1.x), fminf(c0.z, c1.z), fminf(cz.x, cz.z));
+        b.hi = f3(fmaxf(c0.y, c1.y), fmaxf(c0.w, c1.w), fmaxf(cz.y, cz.w));
+    }
+    bool stored = true;  // k_refit_local already wrote this box into its parent's slot
+    while (true) {
+        const uint32_t p = (link >> 1) & kLinkIndexMask, which = link & 1u;
+        if (!stored) store_child_box(nodes + p, which, b);
+        stored = false;
+        __threadfence();
+        if (atomicAdd(visit + p, 1u) == 0u) return;  // sibling not done yet
         const float4 *q = reinterpret_cast<const float4 *>(nodes + p);
         const float4 sxy = __ldcg(q + (which ^ 1u));
         const float2 sz = __ldcg(reinterpret_cast<const float2 *>(q + 2) + (which ^ 1u));
@@ -663,39 +757,9 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
             hi[a] = fmaxf(hi[a], ch[i].hi[a]);
         }
     }
-    // The grid origin sits one step below the node box and every child interval is widened by one
-    // step per side: the traversal's folded FMA may move a plane by half a step (rt_device.cuh qfloat).
-    uint32_t eb[3];
-    uint8_t qlo[3][8], qhi[3][8];
-    float org[3];
-    for (int a = 0; a < 3; a++) {
-        eb[a] = quant_exp((hi[a] - lo[a]) * (255.0f / 252.0f));
-        for (;;) {
-            const float sc = __uint_as_float(eb[a] << 23);
-            org[a] = lo[a] - sc;
-            bool ok = true;
-            for (int i = 0; i < cnt; i++) {
-                // conservative: decoded lo (rounded up) <= child lo, decoded hi (rounded down) >= child hi
-                float ql = fmaxf(floorf((ch[i].lo[a] - org[a]) / sc), 0.0f);
-                if (ql > 0.0f && __fmaf_ru(ql, sc, org[a]) > ch[i].lo[a]) ql -= 1.0f;
-                float qh = fmaxf(ceilf((ch[i].hi[a] - org[a]) / sc), 0.0f);
-                if (__fmaf_rd(qh, sc, org[a]) < ch[i].hi[a]) qh += 1.0f;
-                ql = fmaxf(ql - 1.0f, 0.0f);
-                qh += 1.0f;
-                if (qh > 255.0f || ql > 255.0f) {
-                    ok = false;
-                    break;
-                }
-                qlo[a][i] = (uint8_t)ql;
-                qhi[a][i] = (uint8_t)qh;
-            }
-            if (ok || eb[a] >= 254u) break;
-            eb[a] += 1;
-        }
-    }
-    // slots: octant of the child's centre relative to the node centre (bit0 = +x, bit1 = +y, bit2 = +z)
-    int child_at[8];
-    for (int k = 0; k < 8; k++) child_at[k] = -1;
+    // slots: octant of the child's centre relative to the node centre (bit0 = +x, bit1 = +y, bit2 = +z);
+    // a taken slot falls back to the free slot with the fewest differing bits (lowest index on ties)
+    uint32_t slot_of = 0;  // 4 bits per child
     uint32_t used = 0;
     for (int i = 0; i < cnt; i++) {
         uint32_t want = 0;
@@ -713,45 +777,77 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
             }
         }
         used |= 1u << sl;
-        child_at[sl] = i;
+        slot_of |= sl << (4 * i);
     }
     // every leaf of the binary tree holds exactly one primitive under the wide tree (build_accel)
-    uint32_t imask = 0, leafmask = 0, n_int = 0, n_pr = 0;
-    for (int k = 0; k < 8; k++) {
-        const int i = child_at[k];
-        if (i < 0) continue;
-        if (ch[i].enc >= 0) {
-            imask |= 1u << k;
-            n_int += 1;
-        } else {
-            leafmask |= 1u << k;
-            n_pr += 1;
+    uint32_t imask = 0, leafmask = 0;
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t k = (slot_of >> (4 * i)) & 7u;
+        if (ch[i].enc >= 0) imask |= 1u << k; else leafmask |= 1u << k;
+    }
+    // The grid origin sits one step below the node box and every child interval is widened by one
+    // step per side: the traversal's folded FMA may move a plane by half a step (rt_device.cuh qfloat).
+    // Quantised planes go straight into 64-bit words (byte k = slot k); empty slots keep an inverted
+    // box (lo = 255, hi = 0) and are never hit.
+    unsigned long long empty_lo = 0;
+    for (uint32_t k = 0; k < 8; k++)
+        if (!((used >> k) & 1u)) empty_lo |= 255ull << (8 * k);
+    uint32_t eb[3];
+    unsigned long long qlo64[3], qhi64[3];
+    float org[3];
+    for (int a = 0; a < 3; a++) {
+        eb[a] = quant_exp((hi[a] - lo[a]) * (255.0f / 252.0f));
+        for (;;) {
+            const float sc = __uint_as_float(eb[a] << 23);
+            // 1 / sc is a power of two as well (2^-127 for eb = 254 is a subnormal, still exact), so the
+            // products below are the correctly rounded quotients: identical to dividing, without the
+            // ~15-instruction IEEE division sequence 48 times per node
+            const float isc = __uint_as_float(eb[a] >= 254u ? 0x00400000u : ((254u - eb[a]) << 23));
+            org[a] = lo[a] - sc;
+            bool ok = true;
+            unsigned long long wl = empty_lo, wh = 0;
+            for (int i = 0; i < cnt; i++) {
+                // conservative: decoded lo (rounded up) <= child lo, decoded hi (rounded down) >= child hi
+                float ql = fmaxf(floorf((ch[i].lo[a] - org[a]) * isc), 0.0f);
+                if (ql > 0.0f && __fmaf_ru(ql, sc, org[a]) > ch[i].lo[a]) ql -= 1.0f;
+                float qh = fmaxf(ceilf((ch[i].hi[a] - org[a]) * isc), 0.0f);
+                if (__fmaf_rd(qh, sc, org[a]) < ch[i].hi[a]) qh += 1.0f;
+                ql = fmaxf(ql - 1.0f, 0.0f);
+                qh += 1.0f;
+                if (qh > 255.0f || ql > 255.0f) {
+                    ok = false;
+                    break;
+                }
+                const uint32_t sh = 8u * ((slot_of >> (4 * i)) & 7u);
+                wl |= (unsigned long long)(uint32_t)ql << sh;
+                wh |= (unsigned long long)(uint32_t)qh << sh;
+            }
+            qlo64[a] = wl;
+            qhi64[a] = wh;
+            if (ok || eb[a] >= 254u) break;
+            eb[a] += 1;
         }
     }
+    const uint32_t n_int = __popc(imask), n_pr = __popc(leafmask);
     const uint32_t child_base = n_int ? atomicAdd(&info->n_wnodes, n_int) : 0u;
     const uint32_t prim_base = n_pr ? atomicAdd(&info->n_wprims, n_pr) : 0u;
-    uint32_t px[2] = {0, 0}, py[2] = {0, 0}, pz[2] = {0, 0}, hx[2] = {0, 0}, hy[2] = {0, 0}, hz[2] = {0, 0};
-    uint32_t rank = 0, off = 0;
-    for (int k = 0; k < 8; k++) {
-        const int i = child_at[k];
-        const int sh = 8 * (k & 3);
-        if (i < 0) {  // empty slot: inverted box, never hit
-            px[k >> 2] |= 255u << sh; py[k >> 2] |= 255u << sh; pz[k >> 2] |= 255u << sh;
-            continue;
-        }
-        px[k >> 2] |= (uint32_t)qlo[0][i] << sh; py[k >> 2] |= (uint32_t)qlo[1][i] << sh; pz[k >> 2] |= (uint32_t)qlo[2][i] << sh;
-        hx[k >> 2] |= (uint32_t)qhi[0][i] << sh; hy[k >> 2] |= (uint32_t)qhi[1][i] << sh; hz[k >> 2] |= (uint32_t)qhi[2][i] << sh;
+    // internal children and leaf primitives are stored in slot order
+    for (int i = 0; i < cnt; i++) {
+        const uint32_t k = (slot_of >> (4 * i)) & 7u;
+        const uint32_t below = (1u << k) - 1u;
         if (ch[i].enc >= 0) {
-            wtask[child_base + rank] = (uint32_t)ch[i].enc;
-            rank += 1;
+            wtask[child_base + __popc(imask & below)] = (uint32_t)ch[i].enc;
         } else {
             const uint32_t f = (uint32_t)ch[i].enc & kLeafFirstMask;
-            wslot_geom[prim_base + off] = slot_geom[f];
-            wslot_prim[prim_base + off] = slot_prim[f];
-            wslot_mat[prim_base + off] = slot_mat[f];
-            off += 1;
+            const uint32_t d = prim_base + __popc(leafmask & below);
+            wslot_geom[d] = slot_geom[f];
+            wslot_prim[d] = slot_prim[f];
+            wslot_mat[d] = slot_mat[f];
         }
     }
+    const uint32_t px[2] = {(uint32_t)qlo64[0], (uint32_t)(qlo64[0] >> 32)}, py[2] = {(uint32_t)qlo64[1], (uint32_t)(qlo64[1] >> 32)};
+    const uint32_t pz[2] = {(uint32_t)qlo64[2], (uint32_t)(qlo64[2] >> 32)}, hx[2] = {(uint32_t)qhi64[0], (uint32_t)(qhi64[0] >> 32)};
+    const uint32_t hy[2] = {(uint32_t)qhi64[1], (uint32_t)(qhi64[1] >> 32)}, hz[2] = {(uint32_t)qhi64[2], (uint32_t)(qhi64[2] >> 32)};
     float4 *o = reinterpret_cast<float4 *>(wnodes + w);
     o[0] = make_float4(org[0], org[1], org[2], __uint_as_float(eb[0] | (eb[1] << 8) | (eb[2] << 16) | (imask << 24)));
     o[1] = make_float4(__uint_as_float(child_base), __uint_as_float(prim_base), __uint_as_float(leafmask), 0.0f);
@@ -760,11 +856,34 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
     o[4] = make_float4(__uint_as_float(hy[0]), __uint_as_float(hy[1]), __uint_as_float(hz[0]), __uint_as_float(hz[1]));
 }
 
+// Grid-wide barrier between the levels of k_collapse (the kernel is launched cooperatively, so all blocks
+// are co-resident).  One barrier per level: the LAST block to arrive publishes the end of the next level
+// (BuildInfo.level_end = n_wnodes) before it releases the others, so nobody can observe allocations made
+// by blocks that already run ahead into the next level.  bar[0] counts arrivals (monotonic), bar[1] is
+// the generation; both are zeroed by k_decide at the start of every build.
+__device__ __forceinline__ uint32_t collapse_barrier(BuildInfo *info, uint32_t gen) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile uint32_t *vgen = &info->pad2_[1];
+        __threadfence();
+        const uint32_t arrived = atomicAdd(&info->pad2_[0], 1u) + 1u;
+        if (arrived == gridDim.x * (gen + 1u)) {
+            info->level_end = *reinterpret_cast<volatile uint32_t *>(&info->n_wnodes);
+            __threadfence();
+            *vgen = gen + 1u;
+        } else {
+            while (*vgen <= gen) __nanosleep(64);
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    return *reinterpret_cast<volatile uint32_t *>(&info->level_end);
+}
+
 __global__ void __launch_bounds__(128)
 k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict__ wtask, WNode *__restrict__ wnodes,
            const float4 *__restrict__ slot_geom, const uint32_t *__restrict__ slot_prim, const uint32_t *__restrict__ slot_mat,
            float4 *__restrict__ wslot_geom, uint32_t *__restrict__ wslot_prim, uint32_t *__restrict__ wslot_mat) {
-    cg::grid_group grid = cg::this_grid();
     const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
     const uint32_t n = info->n_bvh;
     // outlier primitives keep their positions behind the tree's primitives
@@ -773,21 +892,19 @@ k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict
         wslot_prim[n + i] = slot_prim[n + i];
         wslot_mat[n + i] = slot_mat[n + i];
     }
-    if (n == 0) return;  // uniform over the grid
-    if (gtid == 0) {
-        wtask[0] = 0;
-        info->n_wnodes = 1;
-        info->n_wprims = 0;
+    if (n == 0) {  // uniform over the grid
+        if (gtid == 0) info->n_wnodes = 0;
+        return;
     }
-    grid.sync();
-    uint32_t begin = 0, end = 1;
+    // k_decide left n_wnodes = 1 (the root's slot: wide node 0 collapses binary node 0).  Task entries are
+    // read with __ldcg: a 128-byte line of wtask can sit in L1 from an earlier level, when the entries of
+    // this level were not written yet.
+    uint32_t begin = 0, end = 1, gen = 0;
     while (begin < end) {
         for (uint32_t w = begin + gtid; w < end; w += gsize)
-            collapse_one(w, (int)wtask[w], nodes, info, wtask, wnodes, slot_geom, slot_prim, slot_mat, wslot_geom, wslot_prim, wslot_mat);
-        grid.sync();
+            collapse_one(w, w == 0 ? 0 : (int)__ldcg(wtask + w), nodes, info, wtask, wnodes, slot_geom, slot_prim, slot_mat, wslot_geom, wslot_prim, wslot_mat);
         begin = end;
-        end = *reinterpret_cast<volatile uint32_t *>(&info->n_wnodes);
-        grid.sync();
+        end = collapse_barrier(info, gen++);
     }
 }
 
@@ -928,7 +1045,13 @@ int build_accel(Scene *s, cudaStream_t st) {
         // 4 passes: result back in buffer 0
         k_gather<<<gb, 256, 0, st>>>(s->vals[0].p, s->w_geom.p, s->w_mat.p, n, s->slot_geom.p, s->slot_prim.p, s->slot_mat.p);
         k_hierarchy<<<gb, 256, 0, st>>>(s->keys[0].p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, (int)(s->wide ? 1u : (s->leaf_max ? s->leaf_max : 4u)));
-        k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
+        if (s->refit_mode == 1) {
+            k_refit_local<<<div_up(n, kRefitBlock), kRefitBlock, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p);
+            k_refit_top<<<div_up(2 * n, 256), 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
+            s->launches += 1;
+        } else {
+            k_refit<<<gb, 256, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p, s->parent_int.p, s->parent_leaf.p, s->visit.p);
+        }
         s->launches += 3;
     }
     k_small_tree<<<1, 32, 0, st>>>(s->slot_geom.p, s->tri_v12.p, s->info.p, s->nodes.p);

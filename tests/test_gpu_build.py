@@ -71,10 +71,11 @@ def check_tree(st, nodes, prim, keys, world):
 
 
 @pytest.mark.parametrize("n,ntri,ground", [(2, 0, False), (5, 3, False), (64, 16, True), (1000, 200, True), (50000, 0, False)])
-def test_tree_invariants(pkg, synth, n, ntri, ground):
+@pytest.mark.parametrize("refit_mode", [0, 1])
+def test_tree_invariants(pkg, synth, n, ntri, ground, refit_mode):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
     world = scenes.flatten_world(d)
-    gs = scenes.GpuScene(pkg, d, options={"wide": 0})
+    gs = scenes.GpuScene(pkg, d, options={"wide": 0, "refit_mode": refit_mode})
     st, nodes, geom, prim, keys = download(gs, len(world["kind_index"]))
     assert int(st.n_prims) == len(world["kind_index"])
     assert int(st.n_huge) == (1 if ground else 0)
@@ -189,10 +190,11 @@ def check_wide_tree(gs, world):
 
 
 @pytest.mark.parametrize("n,ntri,ground", [(1, 0, False), (2, 0, False), (5, 3, False), (64, 16, True), (1000, 200, True), (30000, 0, False)])
-def test_wide_tree_invariants(pkg, synth, n, ntri, ground):
+@pytest.mark.parametrize("refit_mode", [0, 1])
+def test_wide_tree_invariants(pkg, synth, n, ntri, ground, refit_mode):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
     world = scenes.flatten_world(d)
-    gs = scenes.GpuScene(pkg, d)
+    gs = scenes.GpuScene(pkg, d, options={"refit_mode": refit_mode})
     check_wide_tree(gs, world)
     gs.scene.build()  # rebuild over the same buffers: same invariants
     check_wide_tree(gs, world)
