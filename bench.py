@@ -316,6 +316,13 @@ def run_ours(a):
         trace_step = dv["trace_ms"] / a.steps                   # this rank's traversal-kernel time per step
         n_launch = max(1, int(st.trace_launches))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
+        traffic, traffic_src = None, None
+        try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same workload only)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_extend_wide"]
+            if a.n_spheres == 10_000_000 and a.width == 3840 and a.height == 2160:
+                traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+        except (OSError, KeyError, ValueError):
+            pass
         line = {
             "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
@@ -331,8 +338,10 @@ def run_ours(a):
             "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
                       "n_prims": n_prims, "bytes_per_prim": 224,
                       "hbm_frac": (n_prims * 224 / (dv["build_ms"] * 1e-3) / 1e9 / peak) if dv["build_ms"] > 0 else None},
-            "roofline": {"bound": "hbm", "kernel": "k_primary+k_bounce (BVH traversal)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "k_extend_wide (BVH traversal, primary + bounce launches)", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                         "traffic_unit": "DRAM bytes per launch (ncu)", "traffic_source": traffic_src,
+                         "algorithmic_bytes_per_launch": seg_step * a.steps / n_launch * bseg,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                          "bytes_per_segment": bseg, "segments_per_launch": seg_step * a.steps / n_launch,
                          "avg_launch_ms": dv["trace_ms"] / n_launch, "trace_launches_per_step": n_launch / a.steps,
