@@ -167,8 +167,8 @@ int rt_accel_build(rt_scene scene, void *stream);
  *      particle i:  center_out = particle_scale * base_center + shift_i,  radius_out = particle_scale[0]
  *      * base_radius (uniform scale required for spheres).  Same operation order as rt_transform_mesh
  *      followed by the instance flattening of rt_accel_build, so the results are bit-identical to the
- *      host path.  All pointers are device pointers (float3 / float per particle); outputs may alias
- *      nothing else.  Feed the outputs to rt_scene_add_spheres / rt_scene_update_group. */
+ *      host path.  All pointers are device pointers (float3 / float per particle), 16-byte aligned
+ *      (any cudaMalloc / torch allocation is); outputs may alias nothing else.  Feed the outputs to rt_scene_add_spheres / rt_scene_update_group. */
 int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float *dev_base_radii,
                       const float *dev_velocities, size_t n, float duration, size_t frames_this_file,
                       size_t frame, const float particle_shift[3], const float particle_scale[3],

@@ -79,32 +79,57 @@ __device__ __forceinline__ F3 xform_normal(const float *m, F3 n) {
     return normalize3(v);
 }
 
+constexpr uint32_t kFlatItems = 4;  // primitives per thread of k_flatten
 __global__ void __launch_bounds__(256)
 k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_base, uint32_t n_inst,
           const GroupDev *__restrict__ groups, uint32_t n_prims, float4 *__restrict__ w_geom,
           uint32_t *__restrict__ w_mat, float4 *__restrict__ tri_v12, float4 *__restrict__ tri_nrm,
           uint32_t *__restrict__ bucket_tab) {
     __shared__ uint32_t s_tab[kExtentBuckets * 8];
+    __shared__ InstDev s_inst;
+    __shared__ GroupDev s_group;
+    __shared__ uint32_t s_uniform;
     for (uint32_t i = threadIdx.x; i < kExtentBuckets * 8; i += blockDim.x) {
         const uint32_t f = i & 7u;
         s_tab[i] = (f >= 1 && f <= 3) ? 0xFFFFFFFFu : 0u;
     }
+    // The block's kFlatItems * 256 primitives almost always belong to ONE instance: look it up once and keep
+    // its records in shared memory, so that a thread's first data load does not sit behind a chain of
+    // four dependent global loads (search, instance, group, geometry).
+    const uint32_t blk0 = blockIdx.x * (kFlatItems * 256u);
+    if (threadIdx.x == 0) {
+        uint32_t lo = 0, hi = n_inst;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(inst_base + mid) <= blk0) lo = mid; else hi = mid;
+        }
+        const uint32_t last = min(blk0 + kFlatItems * 256u, n_prims) - 1u;
+        s_uniform = (__ldg(inst_base + lo + 1) > last) ? 1u : 0u;  // inst_base[n_inst] = n_prims
+        s_inst = insts[lo];
+        s_group = groups[insts[lo].group];
+    }
     __syncthreads();
+    const bool uniform = s_uniform != 0u;
 
-    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+#pragma unroll 1
+  for (uint32_t item = 0; item < kFlatItems; item++) {
+    const uint32_t gid = blk0 + item * 256u + threadIdx.x;
     const bool valid = gid < n_prims;
     int bucket = -1;
     F3 c = f3(0, 0, 0);
     if (valid) {
-        // last instance whose prim_base <= gid
-        uint32_t lo = 0, hi = n_inst;
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(inst_base + mid) <= gid) lo = mid; else hi = mid;
+        const InstDev *in = &s_inst;
+        if (!uniform) {
+            // last instance whose prim_base <= gid
+            uint32_t lo = 0, hi = n_inst;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (__ldg(inst_base + mid) <= gid) lo = mid; else hi = mid;
+            }
+            in = insts + lo;
         }
-        const InstDev *in = insts + lo;
         const uint32_t k = gid - in->prim_base;
-        const GroupDev g = groups[in->group];
+        const GroupDev g = uniform ? s_group : groups[in->group];
         const uint32_t mat = in->mat + k * in->mat_stride;
         float4 wg;
         Box3 b;
@@ -170,6 +195,7 @@ k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_b
             atomicMax(t + 4, kx1); atomicMax(t + 5, ky1); atomicMax(t + 6, kz1);
         }
     }
+  }
     __syncthreads();
     for (uint32_t b = threadIdx.x; b < kExtentBuckets; b += blockDim.x) {
         const uint32_t *t = s_tab + b * 8;
@@ -911,28 +937,56 @@ k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict
 // ------------------------------------------------------------------ per-frame particle update (Mesh-mode translation)
 // src/Global/RendererMesh.cu:378-391 + DeviceFunctions.cuh:133-148 with zero rotation, one thread per
 // coordinate so that the float3 arrays are read and written fully coalesced (12 B per particle each way).
+__device__ __forceinline__ float advect1(float c, float v, float duration, float frames, float frame, float sh, float sc) {
+    const float total = v * duration;            // RendererMesh.cu:383
+    const float per_frame = total / frames;      // :386
+    const float shift = sh + per_frame * frame;  // :388
+    return sc * c + shift;                       // row of the 3x4 matrix applied to the centre
+}
+// 4 particles (12 coordinates) per thread: three 128-bit loads per input array, three 128-bit stores
 __global__ void __launch_bounds__(256)
 k_spheres_advect(const float *__restrict__ base_c, const float *__restrict__ base_r, const float *__restrict__ vel, size_t n,
                  float duration, float frames, float frame, F3 pshift, F3 pscale, float *__restrict__ out_c,
                  float *__restrict__ out_r) {
-    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= 3 * n) return;
-    const uint32_t a = (uint32_t)(k % 3);
-    const float sh = a == 0 ? pshift.x : (a == 1 ? pshift.y : pshift.z);
-    const float sc = a == 0 ? pscale.x : (a == 1 ? pscale.y : pscale.z);
-    const float total = vel[k] * duration;       // RendererMesh.cu:383
-    const float per_frame = total / frames;      // :386
-    const float shift = sh + per_frame * frame;  // :388
-    out_c[k] = sc * base_c[k] + shift;           // row a of the 3x4 matrix applied to the centre
-    if (a == 0) out_r[k / 3] = base_r[k / 3] * sqrtf((pscale.x * pscale.x + 0.0f) + 0.0f);  // k_flatten's radius scale
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // quad of particles
+    const size_t p0 = 4 * q;
+    if (p0 >= n) return;
+    const float rs = sqrtf((pscale.x * pscale.x + 0.0f) + 0.0f);  // k_flatten's radius scale
+    const float sh[3] = {pshift.x, pshift.y, pshift.z}, sc[3] = {pscale.x, pscale.y, pscale.z};
+    if (p0 + 4 <= n) {
+        const float4 *c4 = reinterpret_cast<const float4 *>(base_c) + 3 * q;
+        const float4 *v4 = reinterpret_cast<const float4 *>(vel) + 3 * q;
+        float4 *o4 = reinterpret_cast<float4 *>(out_c) + 3 * q;
+        float c[12], v[12];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const float4 a = c4[j], b = v4[j];
+            c[4 * j] = a.x; c[4 * j + 1] = a.y; c[4 * j + 2] = a.z; c[4 * j + 3] = a.w;
+            v[4 * j] = b.x; v[4 * j + 1] = b.y; v[4 * j + 2] = b.z; v[4 * j + 3] = b.w;
+        }
+#pragma unroll
+        for (int j = 0; j < 12; j++) c[j] = advect1(c[j], v[j], duration, frames, frame, sh[j % 3], sc[j % 3]);
+#pragma unroll
+        for (int j = 0; j < 3; j++) o4[j] = make_float4(c[4 * j], c[4 * j + 1], c[4 * j + 2], c[4 * j + 3]);
+        const float4 r = reinterpret_cast<const float4 *>(base_r)[q];
+        reinterpret_cast<float4 *>(out_r)[q] = make_float4(r.x * rs, r.y * rs, r.z * rs, r.w * rs);
+    } else {
+        for (size_t p = p0; p < n; p++) {
+            for (int a = 0; a < 3; a++)
+                out_c[3 * p + a] = advect1(base_c[3 * p + a], vel[3 * p + a], duration, frames, frame, sh[a], sc[a]);
+            out_r[p] = base_r[p] * rs;
+        }
+    }
 }
 
 int spheres_advect(Context *ctx, const float *base_c, const float *base_r, const float *vel, size_t n, float duration,
                    size_t frames, size_t frame, const float *pshift, const float *pscale, float *out_c, float *out_r,
                    cudaStream_t st) {
     if (!n) return RT_OK;
-    const size_t blocks = (3 * n + 255) / 256;
+    const size_t blocks = ((n + 3) / 4 + 255) / 256;
     if (blocks > 0x7FFFFFFFull) return set_error(ctx, RT_ERR_INVALID, "too many particles");
+    if ((((uintptr_t)base_c | (uintptr_t)base_r | (uintptr_t)vel | (uintptr_t)out_c | (uintptr_t)out_r) & 15u) != 0)
+        return set_error(ctx, RT_ERR_INVALID, "rt_spheres_advect: arrays must be 16-byte aligned");
     k_spheres_advect<<<(unsigned)blocks, 256, 0, st>>>(base_c, base_r, vel, n, duration, (float)frames, (float)frame,
                                                       F3{pshift[0], pshift[1], pshift[2]}, F3{pscale[0], pscale[1], pscale[2]},
                                                       out_c, out_r);
@@ -1023,7 +1077,7 @@ int build_accel(Scene *s, cudaStream_t st) {
     RT_CUDA(ctx, cudaMemsetAsync(s->visit.p, 0, n1 * sizeof(uint32_t), st));
     s->launches += 1;
     if (n) {
-        k_flatten<<<gb, 256, 0, st>>>(s->d_insts.p, s->d_inst_base.p, (uint32_t)s->insts.size(), s->d_groups.p, n,
+        k_flatten<<<div_up(n, kFlatItems * 256u), 256, 0, st>>>(s->d_insts.p, s->d_inst_base.p, (uint32_t)s->insts.size(), s->d_groups.p, n,
                                       s->w_geom.p, s->w_mat.p, s->tri_v12.p, s->tri_nrm.p, s->bucket_tab.p);
         s->launches += 1;
     }

@@ -176,12 +176,19 @@ __device__ __forceinline__ void queue_write(const Queue &q, uint32_t i, F3 o, F3
 // block = a few neighbouring pixel tiles).  Results do not depend on queue order (closest hit is
 // order-free, radiance is written by path id), so this is a pure scheduling choice.
 // Must be called by every thread of the block; NW = warps per block.
-constexpr uint32_t kBins = 8;
+constexpr uint32_t kBins = 24;  // capacity; nb = 8 (octant) or 24 (octant x dominant axis) at run time
 __device__ __forceinline__ uint32_t dir_octant(F3 d) {
     return (d.x >= 0.0f ? 1u : 0u) | (d.y >= 0.0f ? 2u : 0u) | (d.z >= 0.0f ? 4u : 0u);
 }
+__device__ __forceinline__ uint32_t dir_bin(F3 d, uint32_t nb) {
+    const uint32_t o = dir_octant(d);
+    if (nb <= 8u) return o;
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    const uint32_t m = (ax >= ay && ax >= az) ? 0u : (ay >= az ? 1u : 2u);
+    return o * 3u + m;
+}
 template <int NW>
-__device__ __forceinline__ uint32_t binned_push(uint32_t *counter, bool emit, uint32_t bin, uint32_t (*s_cnt)[kBins + 1],
+__device__ __forceinline__ uint32_t binned_push(uint32_t *counter, bool emit, uint32_t bin, uint32_t nb, uint32_t (*s_cnt)[kBins + 1],
                                                 uint32_t *s_base) {
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
     const uint32_t key = emit ? bin : kBins;
@@ -192,7 +199,7 @@ __device__ __forceinline__ uint32_t binned_push(uint32_t *counter, bool emit, ui
     __syncthreads();
     if (w == 0) {
         uint32_t tot = 0;
-        if (lane < kBins) {
+        if (lane < nb) {
 #pragma unroll
             for (int ww = 0; ww < NW; ww++) {
                 const uint32_t c = s_cnt[ww][lane];
@@ -202,14 +209,14 @@ __device__ __forceinline__ uint32_t binned_push(uint32_t *counter, bool emit, ui
         }
         uint32_t inc = tot;
 #pragma unroll
-        for (int o = 1; o < (int)kBins; o <<= 1) {
+        for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o);
             if (lane >= (uint32_t)o) inc += t;
         }
         uint32_t base = 0;
-        if (lane == kBins - 1 && inc) base = atomicAdd(counter, inc);
-        base = __shfl_sync(0xFFFFFFFFu, base, kBins - 1);
-        if (lane < kBins) s_base[lane] = base + inc - tot;
+        if (lane == 31u && inc) base = atomicAdd(counter, inc);
+        base = __shfl_sync(0xFFFFFFFFu, base, 31);
+        if (lane < nb) s_base[lane] = base + inc - tot;
     }
     __syncthreads();
     const uint32_t pos = emit ? s_base[key] + s_cnt[w][key] + __popc(peers & ((1u << lane) - 1u)) : 0u;
@@ -284,7 +291,7 @@ constexpr int kPrimaryThreads = 512;
 __global__ void __launch_bounds__(kPrimaryThreads)
 k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
                 const float4 *__restrict__ phit, uint32_t *__restrict__ rng, Queue out, uint32_t *out_count,
-                float4 *__restrict__ result) {
+                float4 *__restrict__ result, uint32_t nb) {
     __shared__ uint32_t s_cnt[kPrimaryThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     uint32_t x, y;
@@ -316,7 +323,7 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
         Scatter sc1;
         Rng r = st;
         if (go) sc1 = scatter(sc, ray, hit, r);
-        const uint32_t qi = binned_push<kPrimaryThreads / 32>(out_count, go, go ? dir_octant(sc1.dir) : 0u, s_cnt, s_base);
+        const uint32_t qi = binned_push<kPrimaryThreads / 32>(out_count, go, go ? dir_bin(sc1.dir, nb) : 0u, nb, s_cnt, s_base);
         if (go) {
             queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, hit.slot, r);
         } else if (valid) {
@@ -341,10 +348,10 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
 // ------------------------------------------------------------------ closest-hit / miss programs over the ray queue
 // One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
 // state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
-constexpr int kShadeThreads = 512;
+template <int kShadeThreads>
 __global__ void __launch_bounds__(kShadeThreads)
 k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
-        uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg) {
+        uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg, uint32_t nb) {
     __shared__ uint32_t s_cnt[kShadeThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     const uint32_t n = *in_count;
@@ -386,7 +393,7 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
                 emit = true;
             }
         }
-        const uint32_t qi = binned_push<kShadeThreads / 32>(out_count, emit, emit ? dir_octant(s.dir) : 0u, s_cnt, s_base);
+        const uint32_t qi = binned_push<kShadeThreads / 32>(out_count, emit, emit ? dir_bin(s.dir, nb) : 0u, nb, s_cnt, s_base);
         if (emit) queue_write(out, qi, s.P, s.dir, thr, pid, slot, r);
     }
 }
@@ -597,14 +604,17 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p);
+            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p, s->ray_bins);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
                 const Queue qin = make_queue(s, d & 1), qout = make_queue(s, (d + 1) & 1);
                 const ExtendIn in{qin.o, qin.d, nullptr};
                 const int rc = launch_extend(s, sd, in, cnt + d, 0, fetch++, s->hit.p, st);
                 if (rc) return rc;
-                k_shade<<<shade_grid, kShadeThreads, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg);
+                if (s->shade_threads >= 1024)
+                    k_shade<1024><<<(uint32_t)ctx->sm_count * 2u, 1024, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins);
+                else
+                    k_shade<512><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins);
                 s->launches += 1;
             }
             const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
