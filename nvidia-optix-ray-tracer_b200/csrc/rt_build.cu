@@ -567,10 +567,12 @@ k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ t
               const uint32_t *__restrict__ parent_int, const uint32_t *__restrict__ parent_leaf) {
     __shared__ float s_box[2][6][kRefitBlock];  // [which child][lo.xyz hi.xyz][node slot]
     __shared__ uint32_t s_visit[kRefitBlock];
-    const uint32_t n = info->n_bvh;
+    __shared__ uint32_t s_link[kRefitBlock];  // parent links of the block's internal nodes: one coalesced load
+    const uint32_t n = info->n_bvh;           // instead of a dependent global load per level of the climb
     const uint32_t b0 = blockIdx.x * kRefitBlock;
     const uint32_t i = b0 + threadIdx.x;
     s_visit[threadIdx.x] = 0;
+    s_link[threadIdx.x] = (i < n) ? parent_int[i] : 0xFFFFFFFFu;
     __syncthreads();
     if (n < 2 || i >= n) return;
     Box3 b = pad_box(prim_box(slot_geom[i], tri_v12));
@@ -584,8 +586,8 @@ k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ t
         const uint32_t p = (link >> 1) & kLinkIndexMask, which = link & 1u;
         store_child_box(nodes + p, which, b);
         if (link & kLinkParentCross) return;  // k_refit_top continues from here
-        const uint32_t next = parent_int[p];  // issued before the hand-over: off the critical path
-        const uint32_t l = p - b0;            // a Karras node's index is one end of its range
+        const uint32_t l = p - b0;  // a Karras node's index is one end of its range: it lies in this block
+        const uint32_t next = s_link[l];
         float(*mine)[kRefitBlock] = s_box[which];
         mine[0][l] = b.lo.x; mine[1][l] = b.lo.y; mine[2][l] = b.lo.z;
         mine[3][l] = b.hi.x; mine[4][l] = b.hi.y; mine[5][l] = b.hi.z;
