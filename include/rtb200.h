@@ -119,9 +119,12 @@ int rt_scene_create(rt_context ctx, rt_scene *out);
 int rt_scene_destroy(rt_scene scene);
 /* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "wide" (1 = traverse
  * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf of
- * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch),
+ * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch; 0 = auto: up to 32 within a third of free memory),
  * "t1" / "t2" / "t3" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
- * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel). */
+ * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "ray_bins" (8 or 24: key of
+ * the per-block grouping of scattered rays: octant, or octant x dominant axis), "shade_threads" (512 or
+ * 1024), "refit_mode" (1 = shared-memory local climb + global top kernel, default; 0 = one kernel with
+ * global counters).  None of them changes a result. */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 
 /* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz

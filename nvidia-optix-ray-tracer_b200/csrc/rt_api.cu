@@ -118,7 +118,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     const std::string k = name;
     if (k == "profile") s.profile = value != 0;
     else if (k == "leaf_max") { s.leaf_max = (uint32_t)std::min<int64_t>(8, std::max<int64_t>(0, value)); s.built = false; }
-    else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(1, value));
+    else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(0, value));
     else if (k == "wide") { s.wide = value != 0; s.built = false; }
     else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "t2") s.t2 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));

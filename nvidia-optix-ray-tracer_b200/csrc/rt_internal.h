@@ -152,7 +152,8 @@ struct Scene {
     bool built = false;
     uint32_t n_prims = 0, n_tris = 0;
     uint32_t leaf_max = 0;        // 0 = auto: 1 primitive per leaf under the 8-wide tree, 4 under the binary LBVH
-    uint32_t batch_spp = 4;
+    uint32_t batch_spp = 0;       // 0 = auto (render_frame)
+    uint32_t auto_batch = 0, auto_batch_npix = 0;
     size_t bytes = 0;
     uint64_t launches = 0;
 
