@@ -150,6 +150,9 @@ int rt_scene_destroy(rt_scene scene) {
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);
+    if (s.ev_fork) cudaEventDestroy(s.ev_fork);
+    if (s.ev_join) cudaEventDestroy(s.ev_join);
+    if (s.aux_stream) cudaStreamDestroy(s.aux_stream);
     delete scene;
     return RT_OK;
 }

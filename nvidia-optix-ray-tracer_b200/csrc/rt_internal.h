@@ -206,6 +206,8 @@ struct Scene {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool have_build_ev = false, have_render_ev = false;
     cudaStream_t last_stream = nullptr;
+    cudaStream_t aux_stream = nullptr;      // side stream for the RNG (re)positioning (render_frame)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     uint64_t last_primary = 0;
     size_t last_n_cnt = 0;
     bool profile = false;

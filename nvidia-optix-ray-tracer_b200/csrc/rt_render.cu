@@ -585,6 +585,34 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
 
     const uint32_t tiles = div_up(W, 8) * div_up(H, 4);
     const uint32_t pix_blocks = div_up(tiles * 32u, 128u);
+    // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 64).  When the per-pixel states have to be
+    // (re)positioned (first frame, or a rank of the spp split whose sample blocks are not contiguous from
+    // frame to frame) that runs on a side stream next to the primary-visibility pass, which does not need them.
+    bool rng_forked = false;
+    if (spp) {
+        const bool base_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
+        const bool cont_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
+                             s->rng_cur_off == (uint64_t)fp->sample_offset;
+        if (!cont_ok) {
+            if (!s->aux_stream) {
+                RT_CUDA(ctx, cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
+                RT_CUDA(ctx, cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+                RT_CUDA(ctx, cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+            }
+            RT_CUDA(ctx, cudaEventRecord(s->ev_fork, st));
+            RT_CUDA(ctx, cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
+            if (!base_ok) {
+                k_rng_init<<<div_up(div_up(npix, kRngRun), 128), 128, 0, s->aux_stream>>>(s->rng_base.p, npix, fp->seed,
+                                                              (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
+                s->launches += 1;
+                s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;
+                s->rng_valid = true;
+            }
+            RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s->aux_stream));
+            RT_CUDA(ctx, cudaEventRecord(s->ev_join, s->aux_stream));
+            rng_forked = true;
+        }
+    }
     // primary visibility: raygen -> closest hit -> ids / AOVs
     k_raygen<<<pix_blocks, 128, 0, st>>>(cd, W, H, s->q_o[0].p, s->q_d[0].p);
     s->launches += 1;
@@ -600,20 +628,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     }
 
     if (spp) {
-        // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 64)
-        const bool base_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
-        const bool cont_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
-                             s->rng_cur_off == (uint64_t)fp->sample_offset;
-        if (!cont_ok) {
-            if (!base_ok) {
-                k_rng_init<<<div_up(div_up(npix, kRngRun), 128), 128, 0, st>>>(s->rng_base.p, npix, fp->seed,
-                                                              (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
-                s->launches += 1;
-                s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;
-                s->rng_valid = true;
-            }
-            RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-        }
+        if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
         const uint32_t shade_grid = (uint32_t)ctx->sm_count * 4u;
         uint32_t done = 0;
         for (uint32_t b = 0; b < n_batches; b++) {
