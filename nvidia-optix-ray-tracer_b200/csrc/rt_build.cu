@@ -461,11 +461,11 @@ k_gather(const uint32_t *__restrict__ vals, const float4 *__restrict__ w_geom, c
 // ------------------------------------------------------------------ K6: Karras (2012) hierarchy
 // delta(i,j) = length of the common prefix of keys i and j; equal keys fall back to the index so
 // the tree is well defined for duplicate Morton codes.
-__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, int j) {
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, uint32_t key_i, int j) {
     if (j < 0 || j >= n) return -1;
-    const uint32_t a = keys[i], b = keys[j];
-    if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
-    return __clz(a ^ b);
+    const uint32_t b = __ldg(keys + j);
+    if (key_i == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clz(key_i ^ b);
 }
 __device__ __forceinline__ int encode_child(int first, int last, int internal_idx, int leaf_max) {
     const int cnt = last - first + 1;
@@ -480,18 +480,19 @@ k_hierarchy(const uint32_t *__restrict__ keys, const BuildInfo *__restrict__ inf
     const int n = (int)info->n_bvh;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (n < 2 || i >= n - 1) return;
-    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
-    const int dmin = delta(keys, n, i, i - d);
+    const uint32_t ki = __ldg(keys + i);
+    const int d = (delta(keys, n, i, ki, i + 1) - delta(keys, n, i, ki, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, ki, i - d);
     int lmax = 2;
-    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    while (delta(keys, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
     int l = 0;
     for (int t = lmax >> 1; t >= 1; t >>= 1)
-        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+        if (delta(keys, n, i, ki, i + (l + t) * d) > dmin) l += t;
     const int j = i + l * d;
-    const int dnode = delta(keys, n, i, j);
+    const int dnode = delta(keys, n, i, ki, j);
     int s = 0;
     for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
-        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (delta(keys, n, i, ki, i + (s + t) * d) > dnode) s += t;
         if (t == 1) break;
     }
     const int split = i + s * d + min(d, 0);
@@ -584,8 +585,10 @@ k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ t
             return;
         }
         const uint32_t p = (link >> 1) & kLinkIndexMask, which = link & 1u;
-        store_child_box(nodes + p, which, b);
-        if (link & kLinkParentCross) return;  // k_refit_top continues from here
+        if (link & kLinkParentCross) {  // k_refit_top continues from here
+            store_child_box(nodes + p, which, b);
+            return;
+        }
         const uint32_t l = p - b0;  // a Karras node's index is one end of its range: it lies in this block
         const uint32_t next = s_link[l];
         float(*mine)[kRefitBlock] = s_box[which];
@@ -595,8 +598,18 @@ k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ t
         if (atomicAdd(&s_visit[l], 1u) == 0u) return;  // the sibling will pick this box up
         __threadfence_block();
         volatile float(*sib)[kRefitBlock] = s_box[which ^ 1u];
-        b.lo = f3(fminf(b.lo.x, sib[0][l]), fminf(b.lo.y, sib[1][l]), fminf(b.lo.z, sib[2][l]));
-        b.hi = f3(fmaxf(b.hi.x, sib[3][l]), fmaxf(b.hi.y, sib[4][l]), fmaxf(b.hi.z, sib[5][l]));
+        Box3 o;
+        o.lo = f3(sib[0][l], sib[1][l], sib[2][l]);
+        o.hi = f3(sib[3][l], sib[4][l], sib[5][l]);
+        {   // the second arriver holds both child boxes: three full 128-bit stores instead of four partial ones
+            const Box3 &c0 = which ? o : b, &c1 = which ? b : o;
+            float4 *q = reinterpret_cast<float4 *>(nodes + p);
+            __stcg(q + 0, make_float4(c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y));
+            __stcg(q + 1, make_float4(c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y));
+            __stcg(q + 2, make_float4(c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z));
+        }
+        b.lo = f3(fminf(b.lo.x, o.lo.x), fminf(b.lo.y, o.lo.y), fminf(b.lo.z, o.lo.z));
+        b.hi = f3(fmaxf(b.hi.x, o.hi.x), fmaxf(b.hi.y, o.hi.y), fmaxf(b.hi.z, o.hi.z));
         link = next;
     }
 }
