@@ -749,6 +749,11 @@ __device__ __forceinline__ void read_children(const Node *__restrict__ nodes, in
     c1.enc = __float_as_int(n3.y);
     c1.lo[0] = n1.x; c1.hi[0] = n1.y; c1.lo[1] = n1.z; c1.hi[1] = n1.w; c1.lo[2] = n2.z; c1.hi[2] = n2.w;
 }
+__device__ __forceinline__ float child_area(const CChild &c) {
+    if (c.enc < 0) return -1.0f;
+    const float dx = c.hi[0] - c.lo[0], dy = c.hi[1] - c.lo[1], dz = c.hi[2] - c.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
 // smallest biased exponent e >= 1 with 255 * 2^(e-127) >= ext
 __device__ __forceinline__ uint32_t quant_exp(float ext) {
     const uint32_t b = __float_as_uint(ext * (1.0f / 255.0f));
@@ -769,23 +774,23 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
         if (c0.lo[0] <= c0.hi[0]) ch[cnt++] = c0;  // the 1-primitive tree has an empty second child
         if (c1.lo[0] <= c1.hi[0]) ch[cnt++] = c1;
     }
+    float area[8];  // half surface area of the internal children, -1 for leaves (never opened)
+    for (int i = 0; i < cnt; i++) area[i] = child_area(ch[i]);
     while (cnt < 8) {
         int bi = -1;
         float ba = -1.0f;
         for (int i = 0; i < cnt; i++) {
-            if (ch[i].enc >= 0) {
-                const float dx = ch[i].hi[0] - ch[i].lo[0], dy = ch[i].hi[1] - ch[i].lo[1], dz = ch[i].hi[2] - ch[i].lo[2];
-                const float ar = dx * dy + dy * dz + dz * dx;
-                if (ar > ba) {
-                    ba = ar;
-                    bi = i;
-                }
+            if (area[i] > ba) {
+                ba = area[i];
+                bi = i;
             }
         }
         if (bi < 0) break;
         CChild c0, c1;
         read_children(nodes, ch[bi].enc, c0, c1);
         ch[bi] = c0;
+        area[bi] = child_area(c0);
+        area[cnt] = child_area(c1);
         ch[cnt++] = c1;
     }
     // node box and per-axis quantisation grid
@@ -808,14 +813,12 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
             if (ch[i].lo[a] + ch[i].hi[a] > lo[a] + hi[a]) want |= 1u << a;
         uint32_t sl = want;
         if ((used >> sl) & 1u) {
-            int bd = 99;
-            for (uint32_t k = 0; k < 8; k++) {
-                const int d = __popc(k ^ want);
-                if (!((used >> k) & 1u) && d < bd) {
-                    bd = d;
-                    sl = k;
-                }
-            }
+            // free slot at Hamming distance 1, else 2, else 3 from `want`, lowest index first
+            const uint32_t fr = ~used & 0xFFu;
+            const uint32_t m1 = (1u << (want ^ 1u)) | (1u << (want ^ 2u)) | (1u << (want ^ 4u));
+            const uint32_t m2 = (1u << (want ^ 3u)) | (1u << (want ^ 5u)) | (1u << (want ^ 6u));
+            const uint32_t c = (fr & m1) ? (fr & m1) : ((fr & m2) ? (fr & m2) : fr);
+            sl = (uint32_t)__ffs(c) - 1u;
         }
         used |= 1u << sl;
         slot_of |= sl << (4 * i);
