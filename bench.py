@@ -367,7 +367,7 @@ def run_ours(a):
         try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same workload only)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_extend_wide"]
             if a.n_spheres == 10_000_000 and a.width == 3840 and a.height == 2160:
-                traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+                traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"] + " (%.0f GB/s of DRAM traffic over that launch: the L2 absorbs the rest)" % tj.get("dram_gbs", 0.0)
         except (OSError, KeyError, ValueError):
             pass
         line = {
