@@ -283,7 +283,13 @@ def run_ours(a):
     sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
     sc.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
     stream = torch.cuda.current_stream().cuda_stream
-    xch = mg.PeerExchange(ctx, npix, rank, world_size, dev) if (world_size > 1 and a.exchange == "peer") else None
+    xch = None
+    if world_size > 1 and a.exchange == "peer":
+        try:
+            xch = mg.PeerExchange(ctx, npix, rank, world_size, dev)
+        except RuntimeError as e:  # raised on every rank together: fall back to the NCCL reduce
+            if rank == 0:
+                print(f"bench.py: {e}; using --exchange nccl", file=sys.stderr)
     # e2e: the particle arrays of frame i+1 travel host -> device on a copy stream while frame i renders
     # (two device buffers, rt_scene_update_group re-points the sphere group each frame; every step still
     # copies its own inputs inside the timed region, one frame ahead)

@@ -108,34 +108,53 @@ class PeerExchange:
     mapped into this process.  Handles travel through torch.distributed (any backend)."""
 
     def __init__(self, ctx, n_pixels: int, rank: int, world: int, device):
+        """Collective over all ranks.  Raises RuntimeError on EVERY rank if any rank could not allocate,
+        export or map a buffer (the collectives below are executed by all ranks regardless, so nobody
+        is left waiting), so that callers can fall back to the NCCL reduce together."""
         import torch
         import torch.distributed as dist
         self.ctx, self.n_pixels, self.rank, self.world, self.device = ctx, n_pixels, rank, world, device
-        self.accum_ptr, h_acc = ctx.peer_alloc(n_pixels * 16)
-        self.frame_ptr, h_frm = ctx.peer_alloc(n_pixels * 4)
-        self.accum = tensor_view(self.accum_ptr, (n_pixels, 4), "float32", device)
-        self.frame = tensor_view(self.frame_ptr, (n_pixels, 4), "uint8", device)
-        self.accum.zero_()
-        self.frame.zero_()
-        mine = torch.frombuffer(bytearray(h_acc + h_frm), dtype=torch.uint8)
+        self.parts, self.frames, self._opened = [], [], []
+        self.accum_ptr = self.frame_ptr = None
+        self.accum = self.frame = None
         nccl = dist.get_backend() == "nccl"
+        self._nccl = nccl
+        err = None
+        h_acc = h_frm = bytes(64)
+        try:
+            self.accum_ptr, h_acc = ctx.peer_alloc(n_pixels * 16)
+            self.frame_ptr, h_frm = ctx.peer_alloc(n_pixels * 4)
+            self.accum = tensor_view(self.accum_ptr, (n_pixels, 4), "float32", device)
+            self.frame = tensor_view(self.frame_ptr, (n_pixels, 4), "uint8", device)
+            self.accum.zero_()
+            self.frame.zero_()
+        except Exception as e:  # noqa: BLE001 - reported to all ranks below
+            err = e
+        mine = torch.frombuffer(bytearray(h_acc + h_frm), dtype=torch.uint8)
         if nccl:
             mine = mine.to(device)
         allh = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(allh, mine)
-        self.parts, self.frames, self._opened = [], [], []
-        for r in range(world):
-            if r == rank:
-                self.parts.append(self.accum_ptr)
-                self.frames.append(self.frame_ptr)
-                continue
-            hb = bytes(allh[r].cpu().numpy().tobytes())
-            a, f = ctx.peer_open(hb[:64]), ctx.peer_open(hb[64:])
-            self.parts.append(a)
-            self.frames.append(f)
-            self._opened += [a, f]
+        if err is None:
+            try:
+                for r in range(world):
+                    if r == rank:
+                        self.parts.append(self.accum_ptr)
+                        self.frames.append(self.frame_ptr)
+                        continue
+                    hb = bytes(allh[r].cpu().numpy().tobytes())
+                    a, f = ctx.peer_open(hb[:64]), ctx.peer_open(hb[64:])
+                    self.parts.append(a)
+                    self.frames.append(f)
+                    self._opened += [a, f]
+            except Exception as e:  # noqa: BLE001
+                err = e
+        ok = torch.tensor([0.0 if err else 1.0], device=device if nccl else "cpu")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         self._token = torch.zeros(1, device=device if nccl else "cpu")
-        self._nccl = nccl
+        if float(ok.item()) < 1.0:
+            self.close()
+            raise RuntimeError(f"peer-memory exchange unavailable on at least one rank ({err!r} on rank {rank})")
 
     def fence(self):
         """Every rank's work enqueued so far is complete before anything enqueued after this runs
@@ -159,11 +178,16 @@ class PeerExchange:
         import torch
         torch.cuda.synchronize()
         for p in self._opened:
-            self.ctx.peer_close(p)
+            try:
+                self.ctx.peer_close(p)
+            except Exception:  # noqa: BLE001 - best effort on the failure path
+                pass
         self._opened = []
         self.accum = self.frame = None
-        self.ctx.peer_free(self.accum_ptr)
-        self.ctx.peer_free(self.frame_ptr)
+        for p in (self.accum_ptr, self.frame_ptr):
+            if p:
+                self.ctx.peer_free(p)
+        self.accum_ptr = self.frame_ptr = None
 
 
 def render_spp_split_peer(scene, xch: PeerExchange, cam, width, height, spp, max_depth, seed, *, frame: int = 0,
