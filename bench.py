@@ -57,6 +57,10 @@ def parse():
     ap.add_argument("--batch-spp", type=int, default=0)
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N>1: per-rank slice sum+resolve over peer memory in one kernel (default) or NCCL reduce to rank 0 + resolve")
+    ap.add_argument("--split-primary", type=int, default=0,
+                    help="N>1 with --exchange peer: each rank traces the primary rays of the whole frame (0, default) or of its pixel "
+                         "slice only (1: measured 0.7 %% slower per frame at N=2 - the extra fence, id<->slot conversion and slice copies "
+                         "cost more than half a primary pass - and it counts the primary segments once instead of N times)")
     ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
     a = ap.parse_args()
     if not a.n_spheres:
@@ -303,7 +307,8 @@ def run_ours(a):
         if e2e:
             pipe.release(step, prefetch)
         if xch is not None:
-            mg.render_spp_split_peer(sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream)
+            mg.render_spp_split_peer(sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream,
+                                     split_primary=bool(a.split_primary))
             if rank == 0 and e2e:
                 h_rgba8.copy_(xch.frame, non_blocking=True)
             return
@@ -380,7 +385,7 @@ def run_ours(a):
             "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)"
+            "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
                        "step": "LBVH rebuild + render + resolve", "primary_rays": "traced once per pixel (no jitter in the reference), counted once"},

@@ -182,6 +182,18 @@ int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float
 int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *params,
               const rt_outputs *out, void *stream);
 
+/* ---- primary visibility for a pixel range (multi-GPU spp split; no counterpart in the reference):
+ *      rt_render_primary traces the camera rays (Shader.cu:246-267) of pixels [first_pixel, first_pixel +
+ *      n_pixels) and stores one hit record per pixel (float4: t, bits(global primitive id or RT_MISS_ID),
+ *      u, v: independent of the rank and of the build) into dev_hits[first_pixel ...] of a
+ *      float4[width*height] buffer.
+ *      rt_scene_set_primary_hits makes the following rt_render calls take their primary hits from such a
+ *      buffer (complete for the whole frame, same camera and size) instead of tracing them; NULL restores
+ *      the default.  The image is bit-identical either way. */
+int rt_render_primary(rt_scene scene, const rt_camera *camera, uint32_t width, uint32_t height,
+                      size_t first_pixel, size_t n_pixels, float *dev_hits, void *stream);
+int rt_scene_set_primary_hits(rt_scene scene, const float *dev_hits);
+
 /* ---- display conversion: replaces colorToFloat4 in raygen (Shader.cu:270) and
  *      convertFloat4ToUchar4Kernel (RendererImpl.cu:672-678).  color = accum.rgb / accum.w,
  *      clamp, sRGB OETF.  color_srgb float4[n] and/or rgba8 uchar4[n]; either may be NULL. */

@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
-    "rt_spheres_advect", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
+    "rt_spheres_advect", "rt_render_primary", "rt_scene_set_primary_hits", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
 ]
 RT_MAX_PARTS = 16
 RT_PEER_HANDLE_BYTES = 64
@@ -105,6 +105,8 @@ def lib() -> C.CDLL:
         L.rt_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(FrameParams), C.POINTER(Outputs), vp]
         L.rt_resolve.argtypes = [vp, vp, sz, vp, vp, vp]
         L.rt_spheres_advect.argtypes = [vp, vp, vp, vp, sz, C.c_float, sz, sz, f_p, f_p, vp, vp, vp]
+        L.rt_render_primary.argtypes = [vp, C.POINTER(Camera), u32, u32, sz, sz, vp, vp]
+        L.rt_scene_set_primary_hits.argtypes = [vp, vp]
         L.rt_peer_alloc.argtypes = [vp, sz, C.POINTER(vp), C.c_char_p]
         L.rt_peer_free.argtypes = [vp, vp]
         L.rt_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
@@ -265,6 +267,12 @@ class Scene:
         fp = FrameParams(width, height, spp, max_depth, seed, sample_offset, (C.c_float * 3)(*background), flags)
         out = Outputs(accum, albedo, normal, prim_id)
         self.ctx.check(lib().rt_render(self._h, C.byref(cam), C.byref(fp), C.byref(out), stream))
+
+    def render_primary(self, cam: Camera, width, height, first_pixel, n_pixels, hits_ptr, stream=None):
+        self.ctx.check(lib().rt_render_primary(self._h, C.byref(cam), width, height, first_pixel, n_pixels, hits_ptr, stream))
+
+    def set_primary_hits(self, hits_ptr):
+        self.ctx.check(lib().rt_scene_set_primary_hits(self._h, hits_ptr))
 
     def trace_rays(self, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream=None):
         self.ctx.check(lib().rt_trace_rays(self._h, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream))

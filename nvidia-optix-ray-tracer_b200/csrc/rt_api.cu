@@ -146,7 +146,7 @@ int rt_scene_destroy(rt_scene scene) {
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();
     s.wnodes.release(); s.wslot_geom.release(); s.wslot_prim.release(); s.wslot_mat.release();
-    s.phit.release(); s.hit.release(); s.u_skip.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
+    s.phit.release(); s.hit.release(); s.u_skip.release(); s.prim_fetch.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);
@@ -270,6 +270,19 @@ int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *pa
     if (!scene || !camera || !params || !out) return RT_ERR_INVALID;
     DeviceGuard g(scene->s.ctx->device);
     return render_frame(&scene->s, camera, params, out, (cudaStream_t)stream);
+}
+
+int rt_render_primary(rt_scene scene, const rt_camera *camera, uint32_t width, uint32_t height, size_t first_pixel,
+                      size_t n_pixels, float *dev_hits, void *stream) {
+    if (!scene || !camera || (n_pixels && !dev_hits)) return RT_ERR_INVALID;
+    DeviceGuard g(scene->s.ctx->device);
+    return render_primary(&scene->s, camera, width, height, first_pixel, n_pixels, dev_hits, (cudaStream_t)stream);
+}
+
+int rt_scene_set_primary_hits(rt_scene scene, const float *dev_hits) {
+    if (!scene) return RT_ERR_INVALID;
+    scene->s.ext_phit = reinterpret_cast<const float4 *>(dev_hits);
+    return RT_OK;
 }
 
 int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *dev_color_srgb, uint8_t *dev_rgba8, void *stream) {

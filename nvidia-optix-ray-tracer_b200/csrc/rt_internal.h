@@ -195,6 +195,8 @@ struct Scene {
     DevBuf<uint32_t> q_r4[2];
     DevBuf<float4> result;        // per path
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
+    const float4 *ext_phit = nullptr;  // caller-supplied primary hit records (rt_scene_set_primary_hits)
+    DevBuf<uint32_t> prim_fetch;        // fetch counter of rt_render_primary
     DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
     uint32_t t1 = 16, t2 = 4, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
     uint32_t extend_blocks_per_sm = 7;
@@ -229,6 +231,8 @@ int set_error(Context *ctx, int code, const char *fmt, ...);
 int build_accel(Scene *s, cudaStream_t stream);
 int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *p, const rt_outputs *out,
                  cudaStream_t stream);
+int render_primary(Scene *s, const rt_camera *cam, uint32_t W, uint32_t H, size_t first, size_t count, float *hits_out,
+                   cudaStream_t stream);
 int resolve(Context *ctx, const float *accum, size_t n, float *color, uint8_t *rgba8, cudaStream_t stream);
 int resolve_parts(Context *ctx, const float *const *parts, int n_parts, size_t first, size_t n, float *sum_out, float *color,
                   uint8_t *rgba8, cudaStream_t stream);

@@ -463,6 +463,26 @@ __global__ void k_invert_slots(const uint32_t *__restrict__ slot_prim, uint32_t 
     if (i < n) gid_to_slot[slot_prim[i]] = i;
 }
 
+// primary hit records in their rank-independent form: slot (position in THIS build's re-packed primitive
+// arrays; the collapse allocates with atomics, so it differs from build to build) <-> global primitive id
+__global__ void k_export_hits(const uint32_t *__restrict__ slot_prim, float4 *__restrict__ hits, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 h = hits[i];
+    const uint32_t slot = __float_as_uint(h.y);
+    h.y = __uint_as_float(slot == kNoSlot ? RT_MISS_ID : __ldg(slot_prim + slot));
+    hits[i] = h;
+}
+__global__ void k_import_hits(const float4 *__restrict__ ext, const uint32_t *__restrict__ gid_to_slot, uint32_t n,
+                              float4 *__restrict__ phit) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 h = ext[i];
+    const uint32_t gid = __float_as_uint(h.y);
+    h.y = __uint_as_float(gid == RT_MISS_ID ? kNoSlot : __ldg(gid_to_slot + gid));
+    phit[i] = h;
+}
+
 // cumulative segment counter (device side, so that no host read is needed between frames)
 __global__ void k_tally(const uint32_t *__restrict__ counters, uint32_t n_cnt, uint32_t primary, unsigned long long *total) {
     if (threadIdx.x || blockIdx.x) return;
@@ -613,16 +633,23 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             rng_forked = true;
         }
     }
-    // primary visibility: raygen -> closest hit -> ids / AOVs
-    k_raygen<<<pix_blocks, 128, 0, st>>>(cd, W, H, s->q_o[0].p, s->q_d[0].p);
-    s->launches += 1;
-    {
+    // primary visibility: raygen -> closest hit -> ids / AOVs; skipped when the caller supplied the hit
+    // records (rt_scene_set_primary_hits: the multi-GPU split traces each pixel's primary ray on ONE rank)
+    const float4 *phit = s->phit.p;
+    if (s->ext_phit) {
+        // vals[1] is free after the build: global id -> slot of this build
+        if (s->n_prims) k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(sd.slot_prim, s->n_prims, s->vals[1].p);
+        k_import_hits<<<div_up(npix, 256), 256, 0, st>>>(s->ext_phit, s->vals[1].p, npix, s->phit.p);
+        s->launches += 2;
+    } else {
+        k_raygen<<<pix_blocks, 128, 0, st>>>(cd, W, H, s->q_o[0].p, s->q_d[0].p);
+        s->launches += 1;
         const ExtendIn in{s->q_o[0].p, s->q_d[0].p, nullptr};
         const int rc = launch_extend(s, sd, in, nullptr, npix, fetch++, s->phit.p, st);
         if (rc) return rc;
     }
     if (out->prim_id || out->albedo || out->normal) {
-        k_primary_aov<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, s->phit.p, out->prim_id, reinterpret_cast<float4 *>(out->albedo),
+        k_primary_aov<<<pix_blocks, 128, 0, st>>>(sd, cd, W, H, phit, out->prim_id, reinterpret_cast<float4 *>(out->albedo),
                                                   reinterpret_cast<float4 *>(out->normal));
         s->launches += 1;
     }
@@ -634,7 +661,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, s->phit.p, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p, s->ray_bins);
+            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p, s->ray_bins);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
                 const Queue qin = make_queue(s, d & 1), qout = make_queue(s, (d + 1) & 1);
@@ -654,14 +681,56 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         }
         s->rng_cur_off = (uint64_t)fp->sample_offset + spp;
     }
-    k_tally<<<1, 32, 0, st>>>(s->counters.p, (uint32_t)n_cnt, npix, s->seg_total.p);
+    const uint32_t n_primary = s->ext_phit ? 0u : npix;  // supplied primaries were counted by rt_render_primary
+    k_tally<<<1, 32, 0, st>>>(s->counters.p, (uint32_t)n_cnt, n_primary, s->seg_total.p);
     s->launches += 1;
     RT_CUDA(ctx, cudaEventRecord(s->ev[3], st));
     RT_CUDA(ctx, cudaGetLastError());
     s->have_render_ev = true;
     s->last_stream = st;
-    s->last_primary = npix;
+    s->last_primary = n_primary;
     s->last_n_cnt = n_cnt;
+    return RT_OK;
+}
+
+// Primary visibility of the pixel range [first, first + count) only: hit records (t, slot, u, v) into
+// hits_out[first ...], indexed by absolute pixel.  Used by the multi-GPU spp split, where every rank
+// would otherwise repeat the same primary pass.
+int render_primary(Scene *s, const rt_camera *cam, uint32_t W, uint32_t H, size_t first, size_t count, float *hits_out, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_render_primary before rt_accel_build");
+    if (!W || !H || (uint64_t)W * H >= (1ull << 31)) return set_error(ctx, RT_ERR_INVALID, "bad image size %ux%u", W, H);
+    const uint32_t npix = W * H;
+    if (first > npix || count > npix - first) return set_error(ctx, RT_ERR_INVALID, "pixel range outside the frame");
+    if (!count) return RT_OK;
+    for (int k = 0; k < 2; k++) {
+        const size_t qk = k == 0 ? (size_t)npix : (s->q_o[1].cap ? s->q_o[1].cap : 1);
+        RT_CUDA(ctx, s->q_o[k].reserve(qk, &s->bytes));
+        RT_CUDA(ctx, s->q_d[k].reserve(qk, &s->bytes));
+    }
+    RT_CUDA(ctx, s->prim_fetch.reserve(1, &s->bytes));
+    if (!s->seg_total.p) {
+        RT_CUDA(ctx, s->seg_total.reserve(1, &s->bytes));
+        RT_CUDA(ctx, cudaMemsetAsync(s->seg_total.p, 0, sizeof(unsigned long long), st));
+    }
+    RT_CUDA(ctx, cudaMemsetAsync(s->prim_fetch.p, 0, sizeof(uint32_t), st));
+    const SceneDev sd = scene_dev(s);
+    CamDev cd;
+    cd.c = F3{cam->center[0], cam->center[1], cam->center[2]};
+    cd.U = F3{cam->U[0], cam->U[1], cam->U[2]};
+    cd.V = F3{cam->V[0], cam->V[1], cam->V[2]};
+    cd.W = F3{cam->W[0], cam->W[1], cam->W[2]};
+    const uint32_t tiles = div_up(W, 8) * div_up(H, 4);
+    k_raygen<<<div_up(tiles * 32u, 128u), 128, 0, st>>>(cd, W, H, s->q_o[0].p, s->q_d[0].p);
+    s->launches += 1;
+    const ExtendIn in{s->q_o[0].p + first, s->q_d[0].p + first, nullptr};
+    const int rc = launch_extend(s, sd, in, nullptr, (uint32_t)count, s->prim_fetch.p, reinterpret_cast<float4 *>(hits_out) + first, st);
+    if (rc) return rc;
+    k_export_hits<<<div_up((uint32_t)count, 256), 256, 0, st>>>(sd.slot_prim, reinterpret_cast<float4 *>(hits_out) + first, (uint32_t)count);
+    k_tally<<<1, 32, 0, st>>>(s->prim_fetch.p, 0u, (uint32_t)count, s->seg_total.p);
+    s->launches += 2;
+    RT_CUDA(ctx, cudaGetLastError());
+    s->last_stream = st;
     return RT_OK;
 }
 

@@ -115,22 +115,25 @@ class PeerExchange:
         import torch.distributed as dist
         self.ctx, self.n_pixels, self.rank, self.world, self.device = ctx, n_pixels, rank, world, device
         self.parts, self.frames, self._opened = [], [], []
-        self.accum_ptr = self.frame_ptr = None
-        self.accum = self.frame = None
+        self.accum_ptr = self.frame_ptr = self.hits_ptr = None
+        self.accum = self.frame = self.hits = None
+        self.peer_hits = []
         nccl = dist.get_backend() == "nccl"
         self._nccl = nccl
         err = None
-        h_acc = h_frm = bytes(64)
+        h_acc = h_frm = h_hit = bytes(64)
         try:
             self.accum_ptr, h_acc = ctx.peer_alloc(n_pixels * 16)
             self.frame_ptr, h_frm = ctx.peer_alloc(n_pixels * 4)
+            self.hits_ptr, h_hit = ctx.peer_alloc(n_pixels * 16)
+            self.hits = tensor_view(self.hits_ptr, (n_pixels, 4), "float32", device)
             self.accum = tensor_view(self.accum_ptr, (n_pixels, 4), "float32", device)
             self.frame = tensor_view(self.frame_ptr, (n_pixels, 4), "uint8", device)
             self.accum.zero_()
             self.frame.zero_()
         except Exception as e:  # noqa: BLE001 - reported to all ranks below
             err = e
-        mine = torch.frombuffer(bytearray(h_acc + h_frm), dtype=torch.uint8)
+        mine = torch.frombuffer(bytearray(h_acc + h_frm + h_hit), dtype=torch.uint8)
         if nccl:
             mine = mine.to(device)
         allh = [torch.empty_like(mine) for _ in range(world)]
@@ -141,12 +144,14 @@ class PeerExchange:
                     if r == rank:
                         self.parts.append(self.accum_ptr)
                         self.frames.append(self.frame_ptr)
+                        self.peer_hits.append(self.hits)
                         continue
                     hb = bytes(allh[r].cpu().numpy().tobytes())
-                    a, f = ctx.peer_open(hb[:64]), ctx.peer_open(hb[64:])
+                    a, f, h = ctx.peer_open(hb[:64]), ctx.peer_open(hb[64:128]), ctx.peer_open(hb[128:192])
                     self.parts.append(a)
                     self.frames.append(f)
-                    self._opened += [a, f]
+                    self.peer_hits.append(tensor_view(h, (n_pixels, 4), "float32", device))
+                    self._opened += [a, f, h]
             except Exception as e:  # noqa: BLE001
                 err = e
         ok = torch.tensor([0.0 if err else 1.0], device=device if nccl else "cpu")
@@ -167,6 +172,22 @@ class PeerExchange:
             torch.cuda.synchronize()
             dist.barrier()
 
+    def gather_primary(self, scene, cam, width, height, stream=None):
+        """Primary visibility split over the ranks: this rank traces the camera rays of its pixel slice
+        (rt_render_primary), then copies the other slices out of the peers' buffers (NVLink reads) and
+        hands the complete frame of hit records to the scene (rt_scene_set_primary_hits), so that the
+        following rt_render does not repeat a pass every rank would otherwise do identically."""
+        first, cnt = pixel_slice(self.n_pixels, self.world, self.rank)
+        scene.render_primary(cam, width, height, first, cnt, self.hits_ptr, stream)
+        self.fence()
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            f, c = pixel_slice(self.n_pixels, self.world, r)
+            if c:
+                self.hits[f:f + c].copy_(self.peer_hits[r][f:f + c], non_blocking=True)
+        scene.set_primary_hits(self.hits_ptr)
+
     def resolve_slice(self, dst: int = 0, stream=None, sum_out_ptr=None):
         """Sum + resolve this rank's pixel slice from all ranks' partial sums into rank `dst`'s frame."""
         first, cnt = pixel_slice(self.n_pixels, self.world, self.rank)
@@ -183,21 +204,29 @@ class PeerExchange:
             except Exception:  # noqa: BLE001 - best effort on the failure path
                 pass
         self._opened = []
-        self.accum = self.frame = None
-        for p in (self.accum_ptr, self.frame_ptr):
+        self.accum = self.frame = self.hits = None
+        self.peer_hits = []
+        for p in (self.accum_ptr, self.frame_ptr, self.hits_ptr):
             if p:
                 self.ctx.peer_free(p)
-        self.accum_ptr = self.frame_ptr = None
+        self.accum_ptr = self.frame_ptr = self.hits_ptr = None
 
 
 def render_spp_split_peer(scene, xch: PeerExchange, cam, width, height, spp, max_depth, seed, *, frame: int = 0,
-                          background=(0.7, 0.8, 0.9), stream=None, dst: int = 0):
+                          background=(0.7, 0.8, 0.9), stream=None, dst: int = 0, split_primary: bool = False):
     """One frame of the spp split with the peer-memory exchange: this rank's sample block goes into its
     own exchange buffer, then every rank sums and resolves its pixel slice into rank `dst`'s RGBA8 frame."""
     off, cnt = frame_sample_offset(frame, spp, xch.world, xch.rank)
-    if cnt:
-        scene.render(cam, width, height, cnt, max_depth, seed, background, off, 0, xch.accum_ptr, None, None, None, stream)
-    else:
-        xch.accum.zero_()
+    split = split_primary and xch.world > 1
+    if split:
+        xch.gather_primary(scene, cam, width, height, stream)
+    try:
+        if cnt:
+            scene.render(cam, width, height, cnt, max_depth, seed, background, off, 0, xch.accum_ptr, None, None, None, stream)
+        else:
+            xch.accum.zero_()
+    finally:
+        if split:
+            scene.set_primary_hits(None)
     xch.resolve_slice(dst, stream)
     return cnt

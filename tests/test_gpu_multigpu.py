@@ -103,7 +103,9 @@ def _peer_worker(rank, world, port, out_dir):
     xch = mg.PeerExchange(gs.ctx, W * H, rank, world, f"cuda:{dev}")
     stream = torch.cuda.current_stream().cuda_stream
     for frame in range(2):
-        mg.render_spp_split_peer(gs.scene, xch, cam, W, H, SPP, DEPTH, SEED, frame=frame, stream=stream)
+        # frame 0 with every rank tracing all primary rays, frame 1 with the primary pass split by pixel slice
+        mg.render_spp_split_peer(gs.scene, xch, cam, W, H, SPP, DEPTH, SEED, frame=frame, stream=stream,
+                                 split_primary=frame == 1)
         torch.cuda.synchronize()
         np.save(os.path.join(out_dir, f"part_{frame}_{rank}.npy"), xch.accum.cpu().numpy())
         if rank == 0:

@@ -202,3 +202,34 @@ def test_resolve_matches_reference_colour(pkg, oracle):
     assert np.abs(u8[1:300].astype(int) - wu.astype(int)).max() <= 1
     assert np.all(col[0, :3] == 0) and np.all(u8[:, 3] == 255)
     ctx.close()
+
+
+def test_supplied_primary_hits_give_the_same_frame(pkg, synth):
+    """rt_render_primary over two pixel ranges + rt_scene_set_primary_hits == the default rt_render
+    (the multi-GPU split traces each pixel's primary ray on one rank only), also after a rebuild that
+    re-packs the primitives differently."""
+    import torch
+    d = scenes.random_scene(pkg, synth, 5000, n_tris=100, seed=12, metal_every=6, with_ground=True)
+    cam = pkg.camera_configure([2.2, 0.1, 0.2], [0, 0, 0], [0, 0, 1], False)
+    w, h = 200, 112
+    gs = scenes.GpuScene(pkg, d)
+    a = gs.render(cam, w, h, 3, 5, 17)
+    hits = torch.zeros((w * h, 4), dtype=torch.float32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    cut = 9001
+    gs.scene.render_primary(cam, w, h, 0, cut, hits.data_ptr(), st)
+    gs.scene.render_primary(cam, w, h, cut, w * h - cut, hits.data_ptr(), st)
+    torch.cuda.synchronize()
+    ids = hits.cpu().numpy()[:, 1].copy().view(np.uint32)
+    assert np.array_equal(ids, a["prim_id"])          # records carry global primitive ids
+    gs.scene.build()                                   # another build: slots may be allocated in another order
+    gs.scene.set_primary_hits(hits.data_ptr())
+    b = gs.render(cam, w, h, 3, 5, 17)
+    gs.scene.set_primary_hits(None)
+    assert np.array_equal(a["prim_id"], b["prim_id"])
+    assert np.array_equal(a["accum"].view(np.uint32), b["accum"].view(np.uint32))
+    assert np.array_equal(a["albedo"], b["albedo"]) and np.array_equal(a["normal"], b["normal"])
+    assert b["segments"] == a["segments"] - w * h      # the supplied primaries are not traced again
+    with pytest.raises(pkg.RtError):
+        gs.scene.render_primary(cam, w, h, w * h - 5, 10, hits.data_ptr(), st)
+    gs.close()
