@@ -349,7 +349,7 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
 // One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
 // state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
 template <int kShadeThreads>
-__global__ void __launch_bounds__(kShadeThreads)
+__global__ void __launch_bounds__(kShadeThreads, kShadeThreads == 512 ? 3 : 1)
 k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
         uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg, uint32_t nb) {
     __shared__ uint32_t s_cnt[kShadeThreads / 32][kBins + 1];
@@ -656,7 +656,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
 
     if (spp) {
         if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
-        const uint32_t shade_grid = (uint32_t)ctx->sm_count * 4u;
+        const uint32_t shade_grid = (uint32_t)ctx->sm_count * 3u;  // 3 resident blocks of 512 threads (40 registers)
         uint32_t done = 0;
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
