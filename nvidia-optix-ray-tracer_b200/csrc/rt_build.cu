@@ -18,6 +18,15 @@
 
 namespace cg = cooperative_groups;
 
+// occupancy targets of the two register-heavy build kernels (min blocks per SM in __launch_bounds__);
+// overridable at build time for experiments: make EXTRA=-DRT_COLLAPSE_MIN_BLOCKS=12
+#ifndef RT_SORT_MIN_BLOCKS
+#define RT_SORT_MIN_BLOCKS 3
+#endif
+#ifndef RT_COLLAPSE_MIN_BLOCKS
+#define RT_COLLAPSE_MIN_BLOCKS 8
+#endif
+
 namespace rtb {
 
 // ------------------------------------------------------------------ small device helpers
@@ -329,7 +338,7 @@ k_sort_hist(const uint32_t *__restrict__ keys, uint32_t n, uint32_t *__restrict_
     }
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, RT_SORT_MIN_BLOCKS)
 k_sort_pass(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
             uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint32_t n, int pass,
             uint32_t *__restrict__ scratch, uint32_t ntiles) {
@@ -924,7 +933,7 @@ __device__ __forceinline__ uint32_t collapse_barrier(BuildInfo *info, uint32_t g
     return *reinterpret_cast<volatile uint32_t *>(&info->level_end);
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, RT_COLLAPSE_MIN_BLOCKS)
 k_collapse(const Node *__restrict__ nodes, BuildInfo *info, uint32_t *__restrict__ wtask, WNode *__restrict__ wnodes,
            const float4 *__restrict__ slot_geom, const uint32_t *__restrict__ slot_prim, const uint32_t *__restrict__ slot_mat,
            float4 *__restrict__ wslot_geom, uint32_t *__restrict__ wslot_prim, uint32_t *__restrict__ wslot_mat) {
