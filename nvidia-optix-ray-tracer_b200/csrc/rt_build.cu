@@ -21,10 +21,10 @@ namespace cg = cooperative_groups;
 // occupancy targets of the two register-heavy build kernels (min blocks per SM in __launch_bounds__);
 // overridable at build time for experiments: make EXTRA=-DRT_COLLAPSE_MIN_BLOCKS=12
 #ifndef RT_SORT_MIN_BLOCKS
-#define RT_SORT_MIN_BLOCKS 3
+#define RT_SORT_MIN_BLOCKS 4
 #endif
 #ifndef RT_COLLAPSE_MIN_BLOCKS
-#define RT_COLLAPSE_MIN_BLOCKS 8
+#define RT_COLLAPSE_MIN_BLOCKS 6
 #endif
 
 namespace rtb {
