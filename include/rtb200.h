@@ -52,8 +52,11 @@ extern "C" {
 /* rt_frame_params.flags */
 #define RT_FLAG_ACCUMULATE 1u /* add this call's samples to accum_linear instead of overwriting */
 
-/* XORWOW draws reserved per (pixel, sample): stream(p, s) = curand_init(seed, p, (offset+s)*64) */
-#define RT_RNG_SAMPLE_STRIDE 64u
+/* XORWOW draws reserved per (pixel, sample): stream(p, s) = curand_init(seed, p, (offset+s)*32).
+ * A path draws at most 3 per bounce, so max_depth <= 11 (the reference's rayTraceDepth is 5,
+ * include/Global/Shader.cuh:8); rt_render rejects deeper paths.  Advancing a pixel's state from one
+ * sample to the next costs one XORWOW step per reserved draw, hence no larger than needed. */
+#define RT_RNG_SAMPLE_STRIDE 32u
 
 typedef struct rt_context_s *rt_context;
 typedef struct rt_scene_s *rt_scene;

@@ -20,7 +20,7 @@ RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_UNSUPPORTED, RT_ERR_STATE
 RT_MAT_ROUGH, RT_MAT_METAL = 0, 1
 RT_MISS_ID = 0xFFFFFFFF
 RT_FLAG_ACCUMULATE = 1
-RT_RNG_SAMPLE_STRIDE = 64
+RT_RNG_SAMPLE_STRIDE = 32
 
 # every symbol include/rtb200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [

@@ -53,7 +53,7 @@ __device__ __forceinline__ Ray primary_ray(const CamDev &cam, uint32_t x, uint32
 
 // ------------------------------------------------------------------ RNG state init (HostFunctions.cu:122-127)
 // seed fixed by the caller (the reference xors clock64() in: quirk 7), subsequence = pixel,
-// offset = sample_offset * 64; bounds-checked and unpadded (quirk 8).
+// offset = sample_offset * RT_RNG_SAMPLE_STRIDE; bounds-checked and unpadded (quirk 8).
 // cuRAND's sequence skip costs ~20 GF(2) matrix-vector products (160x160 bits each) per state.  The
 // states of consecutive pixels differ by ONE application of the sequence-skip matrix
 // S = precalc_xorwow_matrix[0] (state(p+1) = S * state(p): all skips are powers of the same one-step
@@ -605,7 +605,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
 
     const uint32_t tiles = div_up(W, 8) * div_up(H, 4);
     const uint32_t pix_blocks = div_up(tiles * 32u, 128u);
-    // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 64).  When the per-pixel states have to be
+    // RNG: stream(p, s) = curand_init(seed, p, (sample_offset + s) * 32).  When the per-pixel states have to be
     // (re)positioned (first frame, or a rank of the spp split whose sample blocks are not contiguous from
     // frame to frame) that runs on a side stream next to the primary-visibility pass, which does not need them.
     bool rng_forked = false;

@@ -5,7 +5,7 @@ single-GPU, docs/technical-details.md:327).  One process per GPU, `torch.distrib
                  contiguous block of the frame's samples for every pixel; ONE exchange per frame:
                  a sum-reduce of the float4 accumulation buffer to rank 0 (NCCL over NVLink on the
                  GPU box, gloo in the CPU tests).  Sample s of pixel p uses the same XORWOW stream
-                 (seed, p, s*64) whatever the partition, so the image does not depend on the world
+                 (seed, p, s*32) whatever the partition, so the image does not depend on the world
                  size except for the fp32 re-association of the per-rank partial sums.
   frame parallel frame f of a time series goes to rank f mod world; no collective on the data path.
 

@@ -572,7 +572,7 @@ static int render_impl(const orc_scene *sc, const Accel *ac, const orc_camera *c
                 aov.albedo[0] = al[0]; aov.albedo[1] = al[1]; aov.albedo[2] = al[2]; aov.albedo[3] = 1.0f;
                 aov.normal[0] = nn.x; aov.normal[1] = nn.y; aov.normal[2] = nn.z; aov.normal[3] = 0.0f;
             }
-            // stream(pixel, sample) = curand_init(seed, pixel, (sample_offset + s) * 64):
+            // stream(pixel, sample) = curand_init(seed, pixel, (sample_offset + s) * 32):
             // generator/subsequence per pixel as HostFunctions.cu:122-127, seed fixed (quirk 7).
             curandState base;
             curand_init(p->seed, pix, (unsigned long long)p->sample_offset * ORC_RNG_SAMPLE_STRIDE, &base);

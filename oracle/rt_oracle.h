@@ -23,7 +23,7 @@ extern "C" {
 #define ORC_KIND_TRIANGLE 1u
 #define ORC_MAT_ROUGH 0u
 #define ORC_MAT_METAL 1u
-#define ORC_RNG_SAMPLE_STRIDE 64u
+#define ORC_RNG_SAMPLE_STRIDE 32u
 
 /* World-space (flattened) scene.  Global primitive id = index into kind_index[]. */
 typedef struct {

@@ -131,7 +131,7 @@ def test_oracle_bvh_equals_brute_force_on_random_rays(pkg, synth, oracle, built_
 
 
 def test_sample_partition_independence(pkg, synth, oracle, built_lib):
-    """stream(p, s) = curand_init(seed, p, (offset+s)*64): rendering samples [0,4) equals rendering
+    """stream(p, s) = curand_init(seed, p, (offset+s)*32): rendering samples [0,4) equals rendering
     [0,2) and [2,4) separately and adding — the property the multi-GPU spp split relies on."""
     d = scenes.random_scene(pkg, synth, 200, seed=5)
     w = scenes.flatten_world(d)
