@@ -1,5 +1,5 @@
 #!/bin/bash
-# r2m: C4 only, final code: scaling on one 8-GPU box: C4 (spp split, peer exchange) at N=1,2,4,8 and C5 (frame-parallel) at N=1,8
+# r2m / r2p: C4 only, final code: scaling on one 8-GPU box: C4 (spp split, peer exchange) at N=1,2,4,8 and C5 (frame-parallel) at N=1,8
 mkdir -p gpurun_out
 nvidia-smi -L | head -8; free -g | head -2
 for n in 1 2 4 8; do
