@@ -388,7 +388,12 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
-                       "step": "LBVH rebuild + render + resolve", "primary_rays": "traced once per pixel (no jitter in the reference), counted once"},
+                       "step": "LBVH rebuild + render + resolve",
+                       "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
+                                       ("" if world_size == 1 else (" per rank: every rank traces the whole primary pass (%.1f %% of the counted segments)"
+                                                                   % (100.0 * npix * world_size * a.steps / max(dv["segs"], 1.0))
+                                                                   if not (xch is not None and a.split_primary) else
+                                                                   "; the primary pass is split by pixel slice across the ranks"))},
             "e2e": {"value": ee["segs"] / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
                     "h2d_bytes_per_step": int(h_centers.numel() * 4 + h_radii.numel() * 4), "d2h_bytes_per_step": int(h_rgba8.numel())},
             "gpu_launches": dv["launches"] * world_size,
