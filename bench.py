@@ -381,21 +381,26 @@ def run_ours(a):
                 traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"] + " (%.0f GB/s of DRAM traffic over that launch: the L2 absorbs the rest)" % tj.get("dram_gbs", 0.0)
         except (OSError, KeyError, ValueError):
             pass
+        # Under the spp split every rank traces the whole primary-visibility pass: those segments are real
+        # work but the same work N times, so the job's throughput counts them ONCE (as the 1-GPU run does).
+        replicated = world_size > 1 and not (xch is not None and a.split_primary)
+        dup = float((world_size - 1) * npix * a.steps) if replicated else 0.0
         line = {
-            "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
+            "metric": "Mrays/s", "value": (dv["segs"] - dup) / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": dv["ms"] / a.steps, "higher_is_better": True,
+            "value_including_replicated_primaries": dv["segs"] / (dv["ms"] * 1e-3) / 1e6,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
                        "step": "LBVH rebuild + render + resolve",
                        "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
-                                       ("" if world_size == 1 else (" per rank: every rank traces the whole primary pass (%.1f %% of the counted segments)"
-                                                                   % (100.0 * npix * world_size * a.steps / max(dv["segs"], 1.0))
+                                       ("" if world_size == 1 else ("; every rank traces the whole primary pass, counted once in value (replicated copies: %.1f %% of the traced segments)"
+                                                                   % (100.0 * dup / max(dv["segs"], 1.0))
                                                                    if not (xch is not None and a.split_primary) else
                                                                    "; the primary pass is split by pixel slice across the ranks"))},
-            "e2e": {"value": ee["segs"] / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
-                    "h2d_bytes_per_step": int(h_centers.numel() * 4 + h_radii.numel() * 4), "d2h_bytes_per_step": int(h_rgba8.numel())},
+            "e2e": {"value": (ee["segs"] - dup) / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
+                    "h2d_bytes_per_step": int(h_centers.numel() * 4 + h_radii.numel() * 4) * world_size, "d2h_bytes_per_step": int(h_rgba8.numel())},
             "gpu_launches": dv["launches"] * world_size,
             "clocks": clocks,
             "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
