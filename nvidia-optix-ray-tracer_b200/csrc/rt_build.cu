@@ -582,7 +582,7 @@ k_refit_local(const float4 *__restrict__ slot_geom, const float4 *__restrict__ t
     const uint32_t b0 = blockIdx.x * kRefitBlock;
     const uint32_t i = b0 + threadIdx.x;
     s_visit[threadIdx.x] = 0;
-    s_link[threadIdx.x] = (i < n) ? parent_int[i] : 0xFFFFFFFFu;
+    s_link[threadIdx.x] = (i + 1u < n) ? parent_int[i] : 0xFFFFFFFFu;  // internal nodes are 0 .. n-2
     __syncthreads();
     if (n < 2 || i >= n) return;
     Box3 b = pad_box(prim_box(slot_geom[i], tri_v12));
