@@ -51,6 +51,14 @@ extern "C" {
 
 /* rt_frame_params.flags */
 #define RT_FLAG_ACCUMULATE 1u /* add this call's samples to accum_linear instead of overwriting */
+/* The two transport details in which the default path deviates from shader/Shader.cu on purpose,
+ * switched back to the reference's behaviour.  With both set (and scene option "compat_shading" = 3 for
+ * translated / rotated instances) rt_render reproduces the reference's own closest-hit / miss programs
+ * bit for bit, given the same closest hits and an IEEE 1/sqrt (tests/test_gpu_refparity.py). */
+#define RT_FLAG_REF_NO_SELF_SKIP 2u  /* scattered rays rely on tmin = 1e-6 alone (Shader.cu:230-233); default: a ray
+                                        never re-hits the primitive it leaves (triangles) / takes the far root (spheres) */
+#define RT_FLAG_REF_MUL_ON_RETURN 4u /* albedo products applied innermost first as the recursion unwinds
+                                        (Shader.cu:236-238); default: throughput multiplied on the way down.  max_depth <= 5 */
 
 /* XORWOW draws reserved per (pixel, sample): stream(p, s) = curand_init(seed, p, (offset+s)*32).
  * A path draws at most 3 per bounce, so max_depth <= 11 (the reference's rayTraceDepth is 5,
@@ -124,10 +132,12 @@ int rt_scene_destroy(rt_scene scene);
  * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf of
  * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch; 0 = auto: up to 32 within a third of free memory),
  * "t1" / "t2" / "t3" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
- * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "ray_bins" (8 or 24: key of
+ * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "compat_shading" (bit 0: sphere normals from the OBJECT-space centre
+ * and radius as shader/Shader.cu:124-132 does although the hit point is in world space, bit 1: triangle vertex normals not rotated with
+ * their instance as Shader.cu:139-142; default 0 = correct world-space shading), "ray_bins" (8 or 24: key of
  * the per-block grouping of scattered rays: octant, or octant x dominant axis), "shade_threads" (512 or
  * 1024), "refit_mode" (1 = shared-memory local climb + global top kernel, default; 0 = one kernel with
- * global counters).  None of them changes a result. */
+ * global counters).  None of them changes a result except "compat_shading". */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 
 /* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz

@@ -13,13 +13,16 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librtb200.so")
+# RTB200_LIB: load another build of the same library (A/B experiments: make -C csrc OUT=... EXTRA=-D...)
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(HERE, "librtb200.so")
 HOST_LIB_PATH = os.path.join(HERE, "librtb200_io.so")
 
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_OOM, RT_ERR_UNSUPPORTED, RT_ERR_STATE = range(6)
 RT_MAT_ROUGH, RT_MAT_METAL = 0, 1
 RT_MISS_ID = 0xFFFFFFFF
 RT_FLAG_ACCUMULATE = 1
+RT_FLAG_REF_NO_SELF_SKIP = 2   # rtb200.h: the reference's transport details (Shader.cu:230-233, 236-238)
+RT_FLAG_REF_MUL_ON_RETURN = 4
 RT_RNG_SAMPLE_STRIDE = 32
 
 # every symbol include/rtb200.h declares (checked by tests/test_abi.py)

@@ -120,6 +120,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     else if (k == "leaf_max") { s.leaf_max = (uint32_t)std::min<int64_t>(8, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(0, value));
     else if (k == "wide") { s.wide = value != 0; s.built = false; }
+    else if (k == "compat_shading") { s.compat = (uint32_t)(value & 3); s.built = false; }
     else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "t2") s.t2 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "t3") s.t3 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
@@ -138,10 +139,10 @@ int rt_scene_destroy(rt_scene scene) {
     DeviceGuard g(s.ctx->device);
     cudaDeviceSynchronize();
     s.d_groups.release(); s.d_insts.release(); s.d_inst_base.release(); s.d_roughs.release(); s.d_metals.release();
-    s.w_geom.release(); s.w_mat.release(); s.tri_v12.release(); s.tri_nrm.release();
+    s.w_geom.release(); s.w_mat.release(); s.w_shade.release(); s.tri_v12.release(); s.tri_nrm.release();
     for (int k = 0; k < 2; k++) {
         s.keys[k].release(); s.vals[k].release();
-        s.q_o[k].release(); s.q_d[k].release(); s.q_t[k].release(); s.q_r[k].release(); s.q_r4[k].release();
+        s.q_o[k].release(); s.q_d[k].release(); s.q_t[k].release(); s.q_r[k].release(); s.q_r4[k].release(); s.q_m[k].release();
     }
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256)
 k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_base, uint32_t n_inst,
           const GroupDev *__restrict__ groups, uint32_t n_prims, float4 *__restrict__ w_geom,
           uint32_t *__restrict__ w_mat, float4 *__restrict__ tri_v12, float4 *__restrict__ tri_nrm,
-          uint32_t *__restrict__ bucket_tab) {
+          uint32_t *__restrict__ bucket_tab, float4 *__restrict__ w_shade, uint32_t compat) {
     __shared__ uint32_t s_tab[kExtentBuckets * 8];
     __shared__ InstDev s_inst;
     __shared__ GroupDev s_group;
@@ -145,6 +145,7 @@ k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_b
         if (g.kind == 0) {
             const F3 oc = f3(g.a[3 * (size_t)k], g.a[3 * (size_t)k + 1], g.a[3 * (size_t)k + 2]);
             const float rr = g.b[k];
+            if (w_shade) w_shade[gid] = make_float4(oc.x, oc.y, oc.z, rr);  // what Shader.cu:124-125 reads (quirk 1)
             if (in->identity) {
                 // identical to xform_point for an identity linear part: ((1*x + 0*y) + 0*z) + t
                 wg = make_float4(oc.x + in->m[3], oc.y + in->m[7], oc.z + in->m[11], rr);
@@ -166,7 +167,7 @@ k_flatten(const InstDev *__restrict__ insts, const uint32_t *__restrict__ inst_b
             const float *nn = g.b + 9 * (size_t)k;
             for (int j = 0; j < 3; j++) {
                 F3 n = f3(nn[3 * j], nn[3 * j + 1], nn[3 * j + 2]);
-                if (!in->identity) n = xform_normal(in->m, n);
+                if (!in->identity && !(compat & 2u)) n = xform_normal(in->m, n);  // compat: Shader.cu:139-142 reads them unrotated (quirk 2)
                 tri_nrm[3 * (size_t)ti + j] = make_float4(n.x, n.y, n.z, 0.0f);
             }
             b.lo = f3(fminf(p0.x, fminf(p1.x, p2.x)), fminf(p0.y, fminf(p1.y, p2.y)), fminf(p0.z, fminf(p1.z, p2.z)));
@@ -1049,6 +1050,21 @@ int build_accel(Scene *s, cudaStream_t st) {
         }
     }
     base[s->insts.size()] = (uint32_t)np;
+    for (size_t i = 0; i < s->insts.size(); i++) {
+        const InstDev &in = s->insts[i];
+        const GroupDev &g = s->groups[in.group];
+        if (g.count) {
+            // material of primitive k = (type, index + k * stride): every index must lie inside the table of its
+            // type (scatter() reads roughs[] / metals[] unchecked) and must not carry into the type bit
+            const uint64_t mi = in.mat & 0x7FFFFFFFu;
+            const uint64_t last = mi + (uint64_t)(g.count - 1) * in.mat_stride;
+            const uint64_t table = (in.mat >> 31) ? s->n_metal : s->n_rough;
+            if (last >= table || last >= (1ull << 31))
+                return set_error(ctx, RT_ERR_INVALID, "instance %zu: material index %llu (first %llu, stride %u, %u primitives) outside the %s table of %llu entries",
+                                 i, (unsigned long long)last, (unsigned long long)mi, in.mat_stride, g.count, (in.mat >> 31) ? "metal" : "rough",
+                                 (unsigned long long)table);
+        }
+    }
     if (np >= (1ull << 27))
         return set_error(ctx, RT_ERR_UNSUPPORTED, "more than 2^27 primitives (%llu)", (unsigned long long)np);
     if (np >= 0x7FFFFFFFull) return set_error(ctx, RT_ERR_UNSUPPORTED, "too many primitives");
@@ -1071,6 +1087,7 @@ int build_accel(Scene *s, cudaStream_t st) {
     const uint32_t sort_blocks = div_up(n ? n : 1, kSortTile);
     RT_CUDA(ctx, s->w_geom.reserve(n1, &s->bytes));
     RT_CUDA(ctx, s->w_mat.reserve(n1, &s->bytes));
+    if (s->compat & 1u) RT_CUDA(ctx, s->w_shade.reserve(n1, &s->bytes));
     RT_CUDA(ctx, s->tri_v12.reserve(2 * (nt ? nt : 1), &s->bytes));
     RT_CUDA(ctx, s->tri_nrm.reserve(3 * (nt ? nt : 1), &s->bytes));
     for (int k = 0; k < 2; k++) {
@@ -1105,7 +1122,8 @@ int build_accel(Scene *s, cudaStream_t st) {
     s->launches += 1;
     if (n) {
         k_flatten<<<div_up(n, kFlatItems * 256u), 256, 0, st>>>(s->d_insts.p, s->d_inst_base.p, (uint32_t)s->insts.size(), s->d_groups.p, n,
-                                      s->w_geom.p, s->w_mat.p, s->tri_v12.p, s->tri_nrm.p, s->bucket_tab.p);
+                                      s->w_geom.p, s->w_mat.p, s->tri_v12.p, s->tri_nrm.p, s->bucket_tab.p,
+                                      (s->compat & 1u) ? s->w_shade.p : nullptr, s->compat);
         s->launches += 1;
     }
     k_decide<<<1, 32, 0, st>>>(s->bucket_tab.p, n, s->info.p);
@@ -1180,6 +1198,7 @@ SceneDev scene_dev(const Scene *s) {
     d.roughs = s->d_roughs.p;
     d.metals = s->d_metals.p;
     d.info = s->info.p;
+    d.shade_geom = (s->compat & 1u) ? s->w_shade.p : nullptr;
     return d;
 }
 

@@ -334,6 +334,25 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 // The stack holds node groups only (8 bytes each).  Children are visited in octant order, which is
 // a heuristic only: every hit child is eventually visited, so the closest hit equals brute force.
 #define RT_WSTACK 64
+// Traversal stack = shared-memory short stack + local-memory overflow.  The first RT_SH_STACK entries of a lane's
+// stack live in shared memory, laid out [entry][thread] so that the 32 lanes of a warp touch 32 consecutive
+// 8-byte words (no bank conflicts, no tag lookups, no L1 write-back traffic); deeper entries — the 8-wide tree
+// over 10^7 primitives is ~8 levels deep and a lane pushes at most one group per level, so they are rare — spill
+// to a per-thread local array.  (Round 1 kept all 64 entries in local memory: 23 % of the kernel's L1 bytes.)
+#ifndef RT_SH_STACK
+#define RT_SH_STACK 12
+#endif
+#define RT_EXTEND_THREADS 128
+struct WideStack {
+    uint2 (*sh)[RT_EXTEND_THREADS];  // [RT_SH_STACK][threads of the block]
+    uint2 ovf[RT_WSTACK - RT_SH_STACK];
+    __device__ __forceinline__ void push(int sp, uint2 e) {
+        if (sp < RT_SH_STACK) sh[sp][threadIdx.x] = e; else ovf[sp - RT_SH_STACK] = e;
+    }
+    __device__ __forceinline__ uint2 pop(int sp) const {
+        return sp < RT_SH_STACK ? sh[sp][threadIdx.x] : ovf[sp - RT_SH_STACK];
+    }
+};
 
 // byte j of w as the float 2^23 + q (exact): the 2^23 is folded into the FMA addend of the slab test.
 // That addend is rounded once, which can move a child plane by up to half a quantisation step; the
@@ -376,7 +395,7 @@ __device__ __forceinline__ void fill_perm_table(uint8_t (*s_perm)[256]) {
 // `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
 __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
                                                  float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic,
-                                                 const uint8_t (*s_perm)[256]) {
+                                                 const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS]) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt = (1u << lane) - 1u;
@@ -385,7 +404,8 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
     const uint32_t n_huge = info->n_huge;
     const bool have_tree = info->n_bvh != 0;
 
-    uint2 stack[RT_WSTACK];
+    WideStack stack;
+    stack.sh = s_stack;
     int sp = 0;
     uint32_t gbase = 0, gmask = 0, pbase = 0, pmask = 0, pbase2 = 0, pmask2 = 0;
     bool huge_done = true, huge_wait = false;
@@ -454,7 +474,7 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
             first = false;
             if (want) {
                 if ((gmask >> 8) == 0) {
-                    const uint2 e = stack[--sp];
+                    const uint2 e = stack.pop(--sp);
                     gbase = e.x;
                     gmask = e.y;
                 }
@@ -462,7 +482,7 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
                 gmask &= ~(1u << bit);
                 const uint32_t slot = (bit - 8u) ^ oct;
                 const uint32_t child = gbase + __popc(gmask & ((1u << slot) - 1u));
-                if (gmask >> 8) stack[sp++] = make_uint2(gbase, gmask);
+                if (gmask >> 8) stack.push(sp++, make_uint2(gbase, gmask));
 
                 const float4 *q = wn + 5 * (size_t)child;
                 const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);

@@ -99,6 +99,9 @@ struct SceneDev {  // everything a traversal needs, passed by value to kernels
     const float4 *roughs;       // rgb _
     const float4 *metals;       // rgb fuzz
     const BuildInfo *info;
+    // compat (option "compat_shading" bit 0): per GLOBAL primitive id, the OBJECT-space
+    // sphere centre + radius the reference's closest-hit program reads (shader/Shader.cu:124-125); NULL = off
+    const float4 *shade_geom;
 };
 
 // ------------------------------------------------------------------ host-side helpers
@@ -167,6 +170,8 @@ struct Scene {
     // build
     DevBuf<float4> w_geom;     // per global prim
     DevBuf<uint32_t> w_mat;    // per global prim
+    DevBuf<float4> w_shade;    // per global prim, compat_shading bit 0 only: object-space sphere centre + radius
+    uint32_t compat = 0;       // option "compat_shading": bit 0 object-space sphere centre (quirk 1), bit 1 unrotated normals (quirk 2)
     DevBuf<float4> tri_v12;    // 2 per tri
     DevBuf<float4> tri_nrm;    // 3 per tri
     DevBuf<uint32_t> keys[2], vals[2];
@@ -193,6 +198,7 @@ struct Scene {
     DevBuf<float4> q_o[2], q_d[2], q_t[2];
     DevBuf<uint4> q_r[2];
     DevBuf<uint32_t> q_r4[2];
+    DevBuf<uint4> q_m[2];         // RT_FLAG_REF_MUL_ON_RETURN only: material words of the path's bounces 1..4
     DevBuf<float4> result;        // per path
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
     const float4 *ext_phit = nullptr;  // caller-supplied primary hit records (rt_scene_set_primary_hits)

@@ -27,6 +27,7 @@ struct Queue {
     float4 *t;    // throughput.rgb, bits(rng.d)
     uint4 *r;     // rng v0..v3
     uint32_t *r4; // rng v4
+    uint4 *m;     // RT_FLAG_REF_MUL_ON_RETURN only (else NULL): material words of the path's bounces 1..4
 };
 
 // ------------------------------------------------------------------ pixel <-> thread mapping (8x4 tiles)
@@ -104,6 +105,7 @@ k_rng_init(uint32_t *__restrict__ rng, uint32_t npix, unsigned long long seed, u
 // ------------------------------------------------------------------ closest-hit shading (Shader.cu:94-242)
 struct Scatter {
     F3 P, dir, alb, N;
+    uint32_t mat;
 };
 __device__ __forceinline__ Scatter scatter(const SceneDev &sc, const Ray &ray, const Hit &hit, Rng &rng) {
     Scatter s;
@@ -111,8 +113,10 @@ __device__ __forceinline__ Scatter scatter(const SceneDev &sc, const Ray &ray, c
     const float4 g = ldg4(sc.slot_geom + hit.slot);
     const uint32_t wb = __float_as_uint(g.w);
     F3 N;
-    if (!(wb & 0x80000000u)) {  // :122-136, world-space centre
-        const F3 on = (s.P - f3(g.x, g.y, g.z)) / g.w;
+    if (!(wb & 0x80000000u)) {  // :122-136, world-space centre (compat: the object-space centre/radius of :124-125)
+        float4 c = g;
+        if (sc.shade_geom) c = ldg4(sc.shade_geom + __ldg(sc.slot_prim + hit.slot));
+        const F3 on = (s.P - f3(c.x, c.y, c.z)) / c.w;
         N = (dot(ray.d, on) < 0.0f) ? on : -on;
     } else {  // :137-155
         const uint32_t ti = wb & 0x7FFFFFFFu;
@@ -146,7 +150,26 @@ __device__ __forceinline__ Scatter scatter(const SceneDev &sc, const Ray &ray, c
     }
     s.dir = dir;
     s.N = N;
+    s.mat = m;
     return s;
+}
+
+// RT_FLAG_REF_MUL_ON_RETURN: radiance of a finished path in the reference's rounding order — the recursion
+// multiplies the albedos innermost first while it unwinds (Shader.cu:236-238): ((bg * a_n) * a_{n-1}) ... * a_1
+__device__ __forceinline__ F3 albedo_of(const SceneDev &sc, uint32_t m) {
+    const float4 a = (m >> 31) ? ldg4(sc.metals + (m & 0x7FFFFFFFu)) : ldg4(sc.roughs + (m & 0x7FFFFFFFu));
+    return f3(a.x, a.y, a.z);
+}
+__device__ __forceinline__ F3 unwind_product(const SceneDev &sc, F3 bg, uint4 mats, uint32_t n) {
+    F3 r = bg;
+    const uint32_t mm[4] = {mats.x, mats.y, mats.z, mats.w};
+#pragma unroll
+    for (int k = 3; k >= 0; k--)
+        if ((uint32_t)k < n) {
+            const F3 a = albedo_of(sc, mm[k]);
+            r = f3(r.x * a.x, r.y * a.y, r.z * a.z);
+        }
+    return r;
 }
 
 // warp-aggregated queue append; returns the slot for lanes with emit == true
@@ -233,13 +256,14 @@ k_extend(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t 
 }
 
 template <int kMinBlocks>
-__global__ void __launch_bounds__(128, kMinBlocks)
+__global__ void __launch_bounds__(RT_EXTEND_THREADS, kMinBlocks)
 k_extend_wide(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint32_t n_fixed, uint32_t *fetch_ctr,
               float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic) {
     __shared__ uint8_t s_perm[8][256];
+    __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
     fill_perm_table(s_perm);
     const uint32_t n = n_ptr ? *n_ptr : n_fixed;
-    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm);
+    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm, s_stack);
 }
 
 // ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
@@ -291,7 +315,7 @@ constexpr int kPrimaryThreads = 512;
 __global__ void __launch_bounds__(kPrimaryThreads)
 k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
                 const float4 *__restrict__ phit, uint32_t *__restrict__ rng, Queue out, uint32_t *out_count,
-                float4 *__restrict__ result, uint32_t nb) {
+                float4 *__restrict__ result, uint32_t nb, uint32_t flags) {
     __shared__ uint32_t s_cnt[kPrimaryThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     uint32_t x, y;
@@ -325,7 +349,9 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
         if (go) sc1 = scatter(sc, ray, hit, r);
         const uint32_t qi = binned_push<kPrimaryThreads / 32>(out_count, go, go ? dir_bin(sc1.dir, nb) : 0u, nb, s_cnt, s_base);
         if (go) {
-            queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, hit.slot, r);
+            // Shader.cu:230-233: the reference relies on tmin alone; by default the ray skips the primitive it leaves
+            queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, (flags & RT_FLAG_REF_NO_SELF_SKIP) ? kNoSlot : hit.slot, r);
+            if (out.m) out.m[qi] = make_uint4(sc1.mat, 0u, 0u, 0u);
         } else if (valid) {
             // miss: 1 * background (Shader.cu:276-287); depth cut-off: 0 (:102-107)
             result[pid] = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
@@ -348,10 +374,10 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
 // ------------------------------------------------------------------ closest-hit / miss programs over the ray queue
 // One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
 // state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
-template <int kShadeThreads>
+template <int kShadeThreads, bool kRefMul>
 __global__ void __launch_bounds__(kShadeThreads, kShadeThreads == 512 ? 3 : 1)
 k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
-        uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg, uint32_t nb) {
+        uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg, uint32_t nb, uint32_t flags) {
     __shared__ uint32_t s_cnt[kShadeThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     const uint32_t n = *in_count;
@@ -364,8 +390,10 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
         Rng r;
         F3 thr;
         uint32_t pid = 0, slot = kNoSlot;
+        uint4 mats = make_uint4(0u, 0u, 0u, 0u);
         if (valid) {
             const float4 o = in.o[i], d = in.d[i], t = in.t[i], hh = hits[i];
+            if (kRefMul) mats = in.m[i];
             Ray ray;
             ray.o = f3(o.x, o.y, o.z);
             ray.d = f3(d.x, d.y, d.z);
@@ -379,7 +407,12 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
             h.u = hh.z;
             h.v = hh.w;
             if (h.slot == kNoSlot) {
-                result[pid] = make_float4(thr.x * bg.x, thr.y * bg.y, thr.z * bg.z, 0.0f);
+                if (kRefMul) {
+                    const F3 rr = unwind_product(sc, bg, mats, depth - 1u);
+                    result[pid] = make_float4(rr.x, rr.y, rr.z, 0.0f);
+                } else {
+                    result[pid] = make_float4(thr.x * bg.x, thr.y * bg.y, thr.z * bg.z, 0.0f);
+                }
             } else if (depth >= max_depth) {
                 result[pid] = make_float4(0, 0, 0, 0);
             } else {
@@ -389,12 +422,18 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
                 r.v4 = in.r4[i];
                 s = scatter(sc, ray, h, r);
                 thr = f3(thr.x * s.alb.x, thr.y * s.alb.y, thr.z * s.alb.z);  // Shader.cu:236-238
-                slot = h.slot;
+                slot = (flags & RT_FLAG_REF_NO_SELF_SKIP) ? kNoSlot : h.slot;
+                if (kRefMul) {
+                    if (depth == 2u) mats.y = s.mat; else if (depth == 3u) mats.z = s.mat; else mats.w = s.mat;
+                }
                 emit = true;
             }
         }
         const uint32_t qi = binned_push<kShadeThreads / 32>(out_count, emit, emit ? dir_bin(s.dir, nb) : 0u, nb, s_cnt, s_base);
-        if (emit) queue_write(out, qi, s.P, s.dir, thr, pid, slot, r);
+        if (emit) {
+            queue_write(out, qi, s.P, s.dir, thr, pid, slot, r);
+            if (kRefMul) out.m[qi] = mats;
+        }
     }
 }
 
@@ -506,7 +545,9 @@ static cudaError_t prof_mark(Scene *s, cudaStream_t st) {
     return cudaEventRecord(s->prof_ev[s->prof_used++], st);
 }
 
-static Queue make_queue(Scene *s, int k) { return Queue{s->q_o[k].p, s->q_d[k].p, s->q_t[k].p, s->q_r[k].p, s->q_r4[k].p}; }
+static Queue make_queue(Scene *s, int k, bool ref_mul = false) {
+    return Queue{s->q_o[k].p, s->q_d[k].p, s->q_t[k].p, s->q_r[k].p, s->q_r4[k].p, ref_mul ? s->q_m[k].p : nullptr};
+}
 
 // one closest-hit pass over a ray buffer; timed when option "profile" is on
 static int launch_extend(Scene *s, const SceneDev &sd, const ExtendIn &in, const uint32_t *n_ptr, uint32_t n_fixed,
@@ -540,6 +581,9 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     if (fp->max_depth > 255) return set_error(ctx, RT_ERR_INVALID, "max_depth %u too large", fp->max_depth);
     if (fp->max_depth > 1 && 3ull * (fp->max_depth - 1) > RT_RNG_SAMPLE_STRIDE)
         return set_error(ctx, RT_ERR_INVALID, "max_depth %u exceeds the RNG stride budget", fp->max_depth);
+    const bool ref_mul = (fp->flags & RT_FLAG_REF_MUL_ON_RETURN) != 0;
+    if (ref_mul && fp->max_depth > 5)
+        return set_error(ctx, RT_ERR_INVALID, "RT_FLAG_REF_MUL_ON_RETURN keeps 4 albedos per path: max_depth <= 5 (the reference's rayTraceDepth)");
     const uint32_t npix = W * H;
     const uint32_t spp = out->accum_linear ? fp->spp : 0u;
     // samples per pixel in flight per wavefront batch: larger batches amortise the drain of the persistent
@@ -576,6 +620,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_r4[k].reserve(qn, &s->bytes));
+            if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qn, &s->bytes));
         }
         RT_CUDA(ctx, s->hit.reserve(qn, &s->bytes));
         RT_CUDA(ctx, s->result.reserve(qn, &s->bytes));
@@ -661,17 +706,19 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, make_queue(s, 0), cnt + 2, s->result.p, s->ray_bins);
+            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, make_queue(s, 0, ref_mul), cnt + 2, s->result.p, s->ray_bins, fp->flags);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
-                const Queue qin = make_queue(s, d & 1), qout = make_queue(s, (d + 1) & 1);
+                const Queue qin = make_queue(s, d & 1, ref_mul), qout = make_queue(s, (d + 1) & 1, ref_mul);
                 const ExtendIn in{qin.o, qin.d, nullptr};
                 const int rc = launch_extend(s, sd, in, cnt + d, 0, fetch++, s->hit.p, st);
                 if (rc) return rc;
-                if (s->shade_threads >= 1024)
-                    k_shade<1024><<<(uint32_t)ctx->sm_count * 2u, 1024, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins);
+                if (ref_mul)
+                    k_shade<512, true><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
+                else if (s->shade_threads >= 1024)
+                    k_shade<1024, false><<<(uint32_t)ctx->sm_count * 2u, 1024, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
                 else
-                    k_shade<512><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins);
+                    k_shade<512, false><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
                 s->launches += 1;
             }
             const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;

@@ -393,8 +393,9 @@ struct Aov {
 inline V3 hit_normal(const orc_scene *sc, const Ray &ray, const Hit &hit, V3 P) {
     const uint32_t ki = sc->kind_index[hit.id];
     const uint32_t idx = ki & 0x7FFFFFFFu;
-    if ((ki >> 31) == ORC_KIND_SPHERE) {  // Shader.cu:122-136 (world-space centre: quirk 1 fixed)
-        const float *s = sc->spheres + 4 * (size_t)idx;
+    if ((ki >> 31) == ORC_KIND_SPHERE) {  // Shader.cu:122-136 (world-space centre: quirk 1 fixed,
+        // unless the scene carries the object-space values the reference's shader reads)
+        const float *s = (sc->sphere_shade ? sc->sphere_shade : sc->spheres) + 4 * (size_t)idx;
         const V3 on = (P - v3(s[0], s[1], s[2])) / s[3];
         return (dot(ray.d, on) < 0.0f) ? on : -on;
     }
@@ -415,9 +416,19 @@ inline void shade_path(const orc_scene *sc, const Accel *ac, const orc_params *p
     Ray ray = primary;
     Hit hit = first;
     uint32_t depth = 1;  // Shader.cu:264 payload.w = 1
+    const bool self_skip = !(p->flags & ORC_FLAG_NO_SELF_SKIP);
+    const bool mul_on_return = (p->flags & ORC_FLAG_MUL_ON_RETURN) != 0;
+    V3 albs[256];  // max_depth <= 255 (checked by the caller)
+    uint32_t n_alb = 0;
     for (;;) {
         if (hit.id == ORC_MISS) {
             // __miss__missProgram, Shader.cu:276-287; albedo products applied on the way back :236-238
+            if (mul_on_return) {  // the reference's order: ((bg * a_n) * a_{n-1}) ... * a_1
+                V3 r = v3(p->background[0], p->background[1], p->background[2]);
+                for (uint32_t k = n_alb; k-- > 0;) r = v3(r.x * albs[k].x, r.y * albs[k].y, r.z * albs[k].z);
+                out_rgb[0] = r.x; out_rgb[1] = r.y; out_rgb[2] = r.z;
+                return;
+            }
             out_rgb[0] = thr.x * p->background[0];
             out_rgb[1] = thr.y * p->background[1];
             out_rgb[2] = thr.z * p->background[2];
@@ -451,7 +462,8 @@ inline void shade_path(const orc_scene *sc, const Accel *ac, const orc_params *p
         // Shader.cu:236-238 — the reference multiplies on the way back up the recursion; we
         // multiply on the way down (same product, rounding order differs by <= depth ulp).
         thr = v3(thr.x * alb.x, thr.y * alb.y, thr.z * alb.z);
-        const uint32_t skip = hit.id;
+        albs[n_alb++] = alb;
+        const uint32_t skip = self_skip ? hit.id : ORC_MISS;
         ray = make_ray(P, dir, kZero, kInf);  // Shader.cu:231-233
         depth += 1;
         hit = closest_hit(sc, ac, ray, skip);
@@ -522,6 +534,22 @@ int orc_num_threads(void) {
 #endif
 }
 
+// bench.py's CPU arms: use every host core whatever OMP_NUM_THREADS says (torchrun exports 1)
+int orc_hw_threads(void) {
+#ifdef _OPENMP
+    return omp_get_num_procs();
+#else
+    return 1;
+#endif
+}
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 void *orc_accel_create(const orc_scene *sc) {
     Accel *a = new Accel;
     build_accel(sc, *a);
@@ -534,13 +562,13 @@ static int render_impl(const orc_scene *sc, const Accel *ac, const orc_camera *c
 
 int orc_render_accel(const orc_scene *sc, const void *accel_handle, const orc_camera *cam, const orc_params *p,
                      float *accum, float *albedo, float *normal, uint32_t *prim_id, uint64_t *segments) {
-    if (!sc || !cam || !p || p->width == 0 || p->height == 0) return 1;
+    if (!sc || !cam || !p || p->width == 0 || p->height == 0 || p->max_depth > 255) return 1;
     return render_impl(sc, static_cast<const Accel *>(accel_handle), cam, p, accum, albedo, normal, prim_id, segments);
 }
 
 int orc_render(const orc_scene *sc, const orc_camera *cam, const orc_params *p, int accel, float *accum,
                float *albedo, float *normal, uint32_t *prim_id, uint64_t *segments) {
-    if (!sc || !cam || !p || p->width == 0 || p->height == 0) return 1;
+    if (!sc || !cam || !p || p->width == 0 || p->height == 0 || p->max_depth > 255) return 1;
     Accel acs;
     const Accel *ac = nullptr;
     if (accel) {
@@ -619,6 +647,14 @@ int orc_trace(const orc_scene *sc, int accel, size_t n_rays, const float *rays, 
         out_id[i] = h.id;
     }
     return 0;
+}
+
+int orc_closest_hit(const orc_scene *sc, const void *accel, const float o[3], const float d[3], float tmin, float tmax,
+                    uint32_t skip, float *t, uint32_t *id, float *u, float *v) {
+    const Ray ray = make_ray(v3(o[0], o[1], o[2]), v3(d[0], d[1], d[2]), tmin, tmax);
+    const Hit h = closest_hit(sc, static_cast<const Accel *>(accel), ray, skip);
+    *t = h.t; *id = h.id; *u = h.u; *v = h.v;
+    return h.id != ORC_MISS;
 }
 
 // src/GraphicsAPI/SDL_GraphicsWindow.cu:4-14 (host code: host rsqrtf semantics)

@@ -24,6 +24,10 @@ extern "C" {
 #define ORC_MAT_ROUGH 0u
 #define ORC_MAT_METAL 1u
 #define ORC_RNG_SAMPLE_STRIDE 32u
+/* orc_params.flags: switch the two transport deviations of DESIGN.md §2 back to the reference's behaviour
+ * (used to pin the oracle against the reference's own shader/Shader.cu, oracle/ref_shader.cpp) */
+#define ORC_FLAG_NO_SELF_SKIP 1u  /* scattered rays rely on tmin = 1e-6 alone (Shader.cu:230-233) */
+#define ORC_FLAG_MUL_ON_RETURN 2u /* albedo products applied innermost first (Shader.cu:236-238)   */
 
 /* World-space (flattened) scene.  Global primitive id = index into kind_index[]. */
 typedef struct {
@@ -36,6 +40,10 @@ typedef struct {
     const float *roughs;        /* 3 floats each                                            */
     const float *metals;        /* 4 floats each: r g b fuzz                                */
     uint32_t n_rough, n_metal;
+    /* Optional (NULL = spheres): 4 floats per sphere, the centre and radius the SHADER sees.  The
+     * reference reads the object-space centre/radius of the hit GAS (shader/Shader.cu:124-125) although
+     * the hit point is in world space (quirk 1); a `compat` scene passes the object-space values here. */
+    const float *sphere_shade;
 } orc_scene;
 
 typedef struct {
@@ -71,6 +79,12 @@ int orc_render_accel(const orc_scene *scene, const void *accel, const orc_camera
 int orc_trace(const orc_scene *scene, int accel, size_t n_rays, const float *rays,
               const uint32_t *skip, float *out_t, uint32_t *out_id);
 
+/* One closest-hit query (the oracle's stand-in for optixTrace's traversal, shader/Shader.cu:70): used
+ * by oracle/ref_shader.cpp to drive the reference's own closest-hit / miss programs.  accel may be
+ * NULL (brute force).  Returns 1 on a hit. */
+int orc_closest_hit(const orc_scene *scene, const void *accel, const float o[3], const float d[3],
+                    float tmin, float tmax, uint32_t skip, float *t, uint32_t *id, float *u, float *v);
+
 /* ---- host-side maths of the path (each mirrors reference host code) ---- */
 void orc_camera_configure(const float center[3], const float target[3], const float up[3],
                           int flip_up, orc_camera *out);
@@ -103,6 +117,8 @@ void orc_xform_normal(const float m12[12], const float n[3], float out[3]);
 uint32_t orc_morton30(float x, float y, float z); /* x,y,z in [0,1] */
 
 int orc_num_threads(void);
+int orc_hw_threads(void);           /* cores visible to this process */
+void orc_set_num_threads(int n);    /* overrides OMP_NUM_THREADS for the following renders */
 
 #ifdef __cplusplus
 }

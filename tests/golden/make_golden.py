@@ -11,6 +11,12 @@ The GPU box has no /root/reference; tests only read the JSON/NPZ files this scri
                            /root/reference by oracle/Makefile) on fixed inputs: constructTransformMatrix,
                            colorToFloat4/Uchar4, SDL_GraphicsWindowConfigureCamera, slerp, quatToEuler,
                            randomSpaceVector over host-compiled cuRAND XORWOW, constants.
+  ref_shader.npz         — outputs of the REFERENCE's own device programs (shader/Shader.cu, unmodified, compiled
+                           as host code by oracle/Makefile -> oracle/_ref/librt_ref_shader.so; its optixTrace asks
+                           the oracle for the closest hit): per scene of scenes.ref_pin_cases() the sum over 4
+                           launches of the linear radiance returned to raygen, plus the sRGB colour buffer and the
+                           (all-zero: SURVEY §C quirk 9) albedo / normal buffers of the last launch for one scene.
+  ref_color_ramp.npz     — include/Util/ColorRamp.cuh bakeColorRamp for every preset (same library).
   oracle_images.npz      — oracle renders of small canned scenes (prim ids + linear accum) so that
                            a change in the oracle itself is caught by the CPU test suite.
 """
@@ -96,12 +102,32 @@ def main():
     cases["constants"] = [float(x) for x in ref.constants()]
     json.dump(cases, open(os.path.join(HERE, "ref_host_math.json"), "w"), indent=0)
 
-    # ---- oracle renders of canned scenes
     import importlib
     pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
     synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
     import scenes
     orc = oracle_lib.load()
+
+    # ---- the reference's shader programs and colour ramps, executed
+    rs = oracle_lib.load_ref_shader()
+    assert rs is not None, "oracle/_ref/librt_ref_shader.so missing (need /root/reference)"
+    W, H, spp, seed = scenes.REF_PIN_SIZE
+    out = {"depth": np.array([rs.trace_depth()], np.uint32)}
+    for name, desc, cam, compat in scenes.ref_pin_cases(pkg, synth):
+        r = rs.render(scenes.flatten_world(desc, compat=compat), cam, W, H, spp, seed)
+        out[name + "_accum"] = r["accum"][:, :3].copy()
+        out[name + "_segments"] = np.array([r["segments"]], np.uint64)
+        if name == "rnd_world":
+            out[name + "_color"] = r["color"]
+        assert not r["albedo"].any() and not r["normal"].any()  # quirk 9, by execution
+    np.savez_compressed(os.path.join(HERE, "ref_shader.npz"), **out)
+    ramps = {}
+    for preset in ("viridis", "plasma", "spectral", "terrain", "heatmap", "grayscale", "TeRRain", "nonsense"):
+        for n in (1, 2, 7, 500):
+            ramps[f"{preset}_{n}"] = rs.bake_color_ramp(preset, n)
+    np.savez_compressed(os.path.join(HERE, "ref_color_ramp.npz"), **ramps)
+
+    # ---- oracle renders of canned scenes
     out = {}
     d = scenes.config1_scene(pkg)
     cam = scenes.config_camera(pkg, "VK")

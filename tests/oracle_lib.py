@@ -12,6 +12,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 LIB = os.path.join(ORACLE_DIR, "_build", "librt_oracle.so")
 REF_LIB = os.path.join(ORACLE_DIR, "_ref", "librt_ref.so")
+REF_SHADER_LIB = os.path.join(ORACLE_DIR, "_ref", "librt_ref_shader.so")
+FLAG_NO_SELF_SKIP = 1   # rt_oracle.h ORC_FLAG_*: the reference's behaviour for the two transport deviations
+FLAG_MUL_ON_RETURN = 2
 
 MISS = 0xFFFFFFFF
 
@@ -19,7 +22,7 @@ MISS = 0xFFFFFFFF
 class OrcScene(C.Structure):
     _fields_ = [("n_prims", C.c_uint32), ("kind_index", C.c_void_p), ("mat", C.c_void_p), ("spheres", C.c_void_p),
                 ("tri_verts", C.c_void_p), ("tri_normals", C.c_void_p), ("roughs", C.c_void_p),
-                ("metals", C.c_void_p), ("n_rough", C.c_uint32), ("n_metal", C.c_uint32)]
+                ("metals", C.c_void_p), ("n_rough", C.c_uint32), ("n_metal", C.c_uint32), ("sphere_shade", C.c_void_p)]
 
 
 class OrcCamera(C.Structure):
@@ -72,14 +75,20 @@ class Oracle:
         """world: dict from scenes.flatten_world() -> (OrcScene, keepalive list)."""
         keep = [np.ascontiguousarray(world[k]) for k in
                 ("kind_index", "mat", "spheres", "tri_verts", "tri_normals", "roughs", "metals")]
-        sc = OrcScene(len(keep[0]), *[a.ctypes.data for a in keep], len(world["roughs"]), len(world["metals"]))
+        shade = world.get("sphere_shade")
+        if shade is not None:
+            shade = np.ascontiguousarray(shade, np.float32)
+            assert shade.shape == keep[2].shape
+            keep.append(shade)
+        sc = OrcScene(len(keep[0]), *[a.ctypes.data for a in keep[:7]], len(world["roughs"]), len(world["metals"]),
+                      shade.ctypes.data if shade is not None else None)
         return sc, keep
 
     def render(self, world, cam, width, height, spp, max_depth, seed, background=(0.7, 0.8, 0.9), sample_offset=0,
-               accel=0, want=("accum", "albedo", "normal", "prim_id")):
+               accel=0, want=("accum", "albedo", "normal", "prim_id"), flags=0):
         sc, keep = self.pack_scene(world)
         oc = OrcCamera(tuple(cam.center), tuple(cam.U), tuple(cam.V), tuple(cam.W))
-        p = OrcParams(width, height, spp, max_depth, seed, sample_offset, (C.c_float * 3)(*background), 0)
+        p = OrcParams(width, height, spp, max_depth, seed, sample_offset, (C.c_float * 3)(*background), flags)
         n = width * height
         out = {
             "accum": np.zeros((n, 4), np.float32) if "accum" in want else None,
@@ -208,6 +217,18 @@ class Oracle:
     def num_threads(self):
         return self.lib.orc_num_threads()
 
+    def hw_threads(self):
+        self.lib.orc_hw_threads.restype = C.c_int
+        return self.lib.orc_hw_threads()
+
+    def set_num_threads(self, n):
+        self.lib.orc_set_num_threads.argtypes = [C.c_int]
+        self.lib.orc_set_num_threads(int(n))
+
+    def closest_hit_address(self):
+        """Address of orc_closest_hit: the traversal callback of oracle/ref_shader.cpp."""
+        return C.cast(self.lib.orc_closest_hit, C.c_void_p)
+
 
 class Ref:
     """oracle/_ref/librt_ref.so — the reference's own header + host functions (see oracle/ref_shim.cu)."""
@@ -266,6 +287,59 @@ class Ref:
         return list(out)
 
 
+class RefShader:
+    """oracle/_ref/librt_ref_shader.so — the reference's UNMODIFIED shader/Shader.cu (raygen, closest-hit, miss
+    programs) and include/Util/ColorRamp.cuh compiled as host code (oracle/ref_shader.cpp); its optixTrace
+    delegates the closest-hit query to the oracle."""
+
+    def __init__(self, lib, oracle: Oracle):
+        self.lib = lib
+        self.orc = oracle
+        lib.ref_shader_render.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_void_p, C.POINTER(OrcCamera), C.POINTER(OrcParams),
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+        lib.ref_bake_color_ramp.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p]
+        lib.ref_preset_name.argtypes = [C.c_char_p]
+        lib.ref_preset_name.restype = C.c_char_p
+        lib.ref_shader_set_rsqrt_mode.argtypes = [C.c_int]
+
+    def trace_depth(self):
+        return self.lib.ref_shader_trace_depth()
+
+    def render(self, world, cam, width, height, spp, seed, background=(0.7, 0.8, 0.9), sample_offset=0, accel=0, rsqrt_mode=0):
+        """spp launches of the reference pipeline; returns linear radiance sum, last launch's colour / AOV buffers."""
+        sc, keep = Oracle.pack_scene(world)
+        acc = None
+        if accel:
+            self.orc.lib.orc_accel_create.restype = C.c_void_p
+            self.orc.lib.orc_accel_create.argtypes = [C.POINTER(OrcScene)]
+            acc = C.c_void_p(self.orc.lib.orc_accel_create(C.byref(sc)))
+        oc = OrcCamera(tuple(cam.center), tuple(cam.U), tuple(cam.V), tuple(cam.W))
+        p = OrcParams(width, height, spp, self.trace_depth(), seed, sample_offset, (C.c_float * 3)(*background), 0)
+        n = width * height
+        out = {k: np.zeros((n, 4), np.float32) for k in ("accum", "color", "albedo", "normal")}
+        seg = C.c_uint64(0)
+        self.lib.ref_shader_set_rsqrt_mode(int(rsqrt_mode))
+        rc = self.lib.ref_shader_render(C.byref(sc), acc, self.orc.closest_hit_address(), C.byref(oc), C.byref(p),
+                                        out["accum"].ctypes.data, out["color"].ctypes.data, out["albedo"].ctypes.data,
+                                        out["normal"].ctypes.data, C.byref(seg))
+        self.lib.ref_shader_set_rsqrt_mode(0)
+        if acc:
+            self.orc.lib.orc_accel_destroy.argtypes = [C.c_void_p]
+            self.orc.lib.orc_accel_destroy(acc)
+        assert rc == 0, rc
+        out["segments"] = seg.value
+        return out
+
+    def bake_color_ramp(self, preset, count):
+        out = np.zeros((count, 3), np.float32)
+        rc = self.lib.ref_bake_color_ramp(preset.encode(), count, out.ctypes.data)
+        assert rc == 0
+        return out
+
+    def preset_name(self, preset):
+        return self.lib.ref_preset_name(preset.encode()).decode()
+
+
 _oracle = None
 
 
@@ -285,3 +359,12 @@ def load_ref():
     if not os.path.exists(REF_LIB):
         return None
     return Ref(C.CDLL(REF_LIB))
+
+
+def load_ref_shader():
+    if not os.path.exists(REF_SHADER_LIB):
+        if os.path.isdir("/root/reference/shader"):
+            build()
+    if not os.path.exists(REF_SHADER_LIB):
+        return None
+    return RefShader(C.CDLL(REF_SHADER_LIB), load())

@@ -68,9 +68,11 @@ def _xform_normals(m, n):
     return out
 
 
-def flatten_world(desc: SceneDesc):
-    """World-space scene for the oracle; global prim id = running index in instance order."""
-    kind_index, mat, spheres, tv, tn = [], [], [], [], []
+def flatten_world(desc: SceneDesc, compat=False):
+    """World-space scene for the oracle; global prim id = running index in instance order.
+    compat=True reproduces what the reference's shader reads: sphere shading uses
+    the OBJECT-space centre/radius (`sphere_shade`), triangle vertex normals are not rotated."""
+    kind_index, mat, spheres, tv, tn, shade = [], [], [], [], [], []
     ns = nt = 0
     for inst in desc.instances:
         g = desc.groups[inst["group"]]
@@ -86,12 +88,13 @@ def flatten_world(desc: SceneDesc):
                 s = np.sqrt((m[0] * m[0] + m[4] * m[4]) + m[8] * m[8])
                 r = g["b"] * f32(s)
             spheres.append(np.concatenate([c, r[:, None]], 1).astype(np.float32))
+            shade.append(np.concatenate([g["a"], g["b"][:, None]], 1).astype(np.float32))
             kind_index.append(np.arange(ns, ns + n, dtype=np.uint32))
             ns += n
         else:
             n = len(g["a"]) // 3
             v = _xform_points(m, g["a"])
-            nn = g["b"] if ident else _xform_normals(m, g["b"])
+            nn = g["b"] if (ident or compat) else _xform_normals(m, g["b"])
             tv.append(v.reshape(n, 9))
             tn.append(nn.reshape(n, 9).astype(np.float32))
             kind_index.append(np.arange(nt, nt + n, dtype=np.uint32) | np.uint32(0x80000000))
@@ -101,6 +104,7 @@ def flatten_world(desc: SceneDesc):
         mat.append(mi | np.uint32(inst["mat_type"] << 31))
     cat = lambda xs, shape, dt: (np.concatenate(xs).astype(dt) if xs else np.zeros(shape, dt))
     return dict(kind_index=cat(kind_index, (0,), np.uint32), mat=cat(mat, (0,), np.uint32),
+                sphere_shade=cat(shade, (0, 4), np.float32) if compat else None,
                 spheres=cat(spheres, (0, 4), np.float32), tri_verts=cat(tv, (0, 9), np.float32),
                 tri_normals=cat(tn, (0, 9), np.float32),
                 roughs=desc.roughs if len(desc.roughs) else np.zeros((1, 3), np.float32),
@@ -252,3 +256,36 @@ def random_scene(pkg, synth, n_spheres, n_tris=0, seed=1, radius=None, metal_eve
         # rotated + translated instance of the soup exercises the non-identity path
         d.add_instance(g, pkg.construct_transform([0.01, -0.02, 0.03], [10, 20, 30], [1, 1, 1]), 1, 1, 0)
     return d
+
+
+# ------------------------------------------------------------------ scenes of the reference pin (tests/golden/ref_shader.npz)
+REF_PIN_SIZE = (64, 36, 4, 20261104)  # width, height, spp, seed; depth = the reference's rayTraceDepth (5)
+
+
+def instanced_scene(pkg, synth):
+    """Translated / rotated / uniformly scaled sphere instances and a rotated triangle instance: the scene on
+    which the reference's object-space shading differs from world-space shading."""
+    ramp = pkg.bake_color_ramp("plasma", 64)
+    d = SceneDesc(np.concatenate([np.asarray(CONFIG_ROUGHS, np.float32), ramp]), [[0.8, 0.85, 0.88, 0.0], [0.9, 0.6, 0.2, 0.25]])
+    c, r = synth.uniform_spheres(40, 0.06, 11)
+    g = d.add_spheres(c * f32(0.8), r)
+    d.add_instance(g, pkg.construct_transform([0.05, -0.1, 0.02], [0, 0, 0], [1, 1, 1]), 0, 4, 1)
+    d.add_instance(g, pkg.construct_transform([-0.2, 0.15, 0.3], [25, -40, 10], [0.5, 0.5, 0.5]), 1, 1, 0)
+    g1 = d.add_spheres([[0, 0, 0]], [0.2])
+    d.add_instance(g1, pkg.construct_transform([0.1, 0.3, -0.25], [0, 0, 0], [1.5, 1.5, 1.5]), 1, 0, 0)
+    v, nn = synth.box_walls(True)
+    gw = d.add_triangles(v, nn)
+    d.add_instance(gw, pkg.construct_transform([0, 0, 0], [0, 0, 15], [1.2, 1.2, 1.2]), 0, 1, 0)
+    return d
+
+
+def ref_pin_cases(pkg, synth):
+    """(name, SceneDesc, camera, compat): compat=True feeds the reference's shader the object-space data it
+    really reads; False feeds it the world-space data of our default shading."""
+    cam1 = config_camera(pkg, "VK")
+    cam2 = pkg.camera_configure([2.2, 0.3, 0.4], [0, 0, 0], [0, 0, 1], False)
+    c1 = config1_scene(pkg)
+    rnd = random_scene(pkg, synth, 300, n_tris=40, seed=3, metal_every=5, fuzz=0.2, with_ground=False)
+    inst = instanced_scene(pkg, synth)
+    return [("c1_compat", c1, cam1, True), ("c1_world", c1, cam1, False), ("rnd_world", rnd, cam2, False),
+            ("rnd_compat", rnd, cam2, True), ("inst_compat", inst, cam2, True), ("inst_world", inst, cam2, False)]
