@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--radius", type=float, default=1.3e-3)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-build-100m", action="store_true", help="skip the C5-size LBVH build entry of the default line")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--leaf-max", type=int, default=0)
     ap.add_argument("--batch-spp", type=int, default=0)
@@ -75,10 +76,30 @@ def workload_name(a):
             f"{a.width}x{a.height}, {a.spp} spp, depth {a.depth}")
 
 
-def build_scene_host(a, pkg, synth):
+TERRAIN_STOPS = [(0.00, (0.149, 0.149, 0.149)), (0.25, (0.114, 0.451, 0.208)), (0.50, (0.639, 0.784, 0.325)),
+                 (0.75, (0.988, 0.972, 0.745)), (1.00, (0.996, 0.922, 0.545))]  # include/Util/ColorRamp.cuh:51-58
+
+
+def terrain_ramp_numpy(count):
+    """bakeColorRamp (ColorRamp.cuh:83-112) for the terrain preset in float32 numpy: the reference arm's material
+    table when neither the product library nor oracle/_ref may be used (colours do not change a segment count)."""
+    f = np.float32
+    u = (np.arange(count, dtype=np.float32) / f(max(count - 1, 1))).astype(np.float32)
+    pos = np.array([p for p, _ in TERRAIN_STOPS], np.float32)
+    col = np.array([c for _, c in TERRAIN_STOPS], np.float32)
+    hi = np.clip(np.searchsorted(pos, u, side="left"), 1, len(pos) - 1)
+    lo = hi - 1
+    t = np.clip((u - pos[lo]) / (pos[hi] - pos[lo]), f(0), f(1)).astype(np.float32)
+    out = (col[lo] + (col[hi] - col[lo]) * t[:, None]).astype(np.float32)
+    if count == 1:
+        out[0] = col[-1]
+    return out
+
+
+def build_scene_host(a, synth, bake_ramp):
     centers, radii = synth.uniform_spheres(a.n_spheres, a.radius, 0x5EED0001)
     wv, wn = synth.box_walls(True)
-    ramp = pkg.bake_color_ramp("terrain", a.n_spheres)
+    ramp = bake_ramp(a.n_spheres)
     roughs = np.concatenate([np.float32([[0.73, 0.73, 0.73]]), ramp]).astype(np.float32)
     metals = np.float32([[0.8, 0.85, 0.88, 0.0]])
     return dict(centers=centers, radii=radii, wall_v=wv, wall_n=wn, roughs=roughs, metals=metals)
@@ -94,11 +115,13 @@ def oracle_world(h):
 
 
 # ---------------------------------------------------------------------------------------------------
-def cpu_sample(a, pkg, host, cam, target_seconds, verbose=False):
-    """Times the CPU oracle (OpenMP over pixel rows, own median-split BVH) on a bounded sample of the
-    same workload: same scene, fewer pixels / samples.  Returns (dict for the JSON line)."""
+def cpu_sample(a, host, cam, target_seconds):
+    """Times the CPU oracle (OpenMP over pixel rows, own median-split BVH, all host cores) on a bounded sample of
+    the same workload: same scene, fewer pixels / samples.  Returns (cpu_baseline dict, the oracle's image of the
+    sample: prim ids + linear sums, its size) so that the caller can bit-compare one rt_render with it."""
     import oracle_lib
     orc = oracle_lib.load()
+    orc.set_num_threads(orc.hw_threads())  # whatever OMP_NUM_THREADS says (torchrun exports 1)
     world = oracle_world(host)
     t0 = time.perf_counter()
     acc = orc.accel_create(world)
@@ -114,34 +137,38 @@ def cpu_sample(a, pkg, host, cam, target_seconds, verbose=False):
     w, h = int(96 * k) // 8 * 8, int(54 * k) // 4 * 4
     w, h = min(w, a.width), min(h, a.height)
     t0 = time.perf_counter()
-    r = orc.render_accel(acc, cam, w, h, spp, a.depth, a.seed)
+    r = orc.render_accel(acc, cam, w, h, spp, a.depth, a.seed, want=("accum", "prim_id"))
     dt = time.perf_counter() - t0
     orc.accel_destroy(acc)
-    return dict(value=r["segments"] / dt / 1e6, unit="Mrays/s", cores=orc.num_threads(), kind="port",
-                sample=f"same scene, {w}x{h}, {spp} spp, depth {a.depth} ({r['segments']} segments in {dt:.1f} s); "
-                       f"oracle BVH build {build_s:.1f} s ({len(world['kind_index']) / build_s / 1e6:.2f} Mprims/s, 1 thread) not in value",
-                build_mprims_s=len(world["kind_index"]) / build_s / 1e6), dt
+    cb = dict(value=r["segments"] / dt / 1e6, unit="Mrays/s", cores=orc.num_threads(), kind="port",
+              sample=f"same scene, {w}x{h}, {spp} spp, depth {a.depth} ({r['segments']} segments in {dt:.1f} s); "
+                     f"oracle BVH build {build_s:.1f} s ({len(world['kind_index']) / build_s / 1e6:.2f} Mprims/s, 1 thread) not in value",
+              build_mprims_s=len(world["kind_index"]) / build_s / 1e6)
+    return cb, r, (w, h, spp)
 
 
 def run_reference(a):
     """--impl reference: the reference's path on the host cores.  The reference itself cannot run here
-    (closed-source OptiX + graphics stack: unavailable on this box), so this arm times the oracle port."""
+    (closed-source OptiX + graphics stack: unavailable on this box), so this arm times the oracle port — and loads
+    nothing of the product: scene from numpy (synth.py), camera and renderer from oracle/."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    pkg = importlib.import_module("nvidia-optix-ray-tracer_b200")
-    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")
-    host = build_scene_host(a, pkg, synth)
-    cam = pkg.camera_configure(**synth.c4_camera())
     import oracle_lib
     orc = oracle_lib.load()
+    orc.set_num_threads(orc.hw_threads())  # all host cores: torchrun exports OMP_NUM_THREADS=1 to its workers
+    synth = importlib.import_module("nvidia-optix-ray-tracer_b200.synth")  # pure numpy; librtb200.so is never loaded here
+    host = build_scene_host(a, synth, terrain_ramp_numpy)
+    c = synth.c4_camera()
+    cam = orc.camera_configure(c["center"], c["target"], c["up"], c["flip_up"])
     world = oracle_world(host)
     tb = time.perf_counter()
     acc = orc.accel_create(world)
     build_s = time.perf_counter() - tb
-    # each step = a bounded sample of the frame: the same view at reduced resolution, 16 spp (high
-    # enough that the one-off per-pixel curand_init is amortised as in the 64-spp workload)
-    w, h, spp = 240, 136, min(16, a.spp)
+    # each step = a bounded sample of the frame: the same view at a quarter of the resolution per axis, 16 spp
+    # (high enough that the one-off per-pixel curand_init is amortised as in the 64-spp workload): ~6 M segments,
+    # about a second of work for 32 threads
+    w, h, spp = a.width // 4, a.height // 4, min(16, a.spp)
     times, segs = [], 0
     for i in range(a.warmup + a.steps):
         t0 = time.perf_counter()
@@ -156,9 +183,11 @@ def run_reference(a):
     line = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": 1e3 * total / max(1, a.steps), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "reference": "CPU oracle port (OptiX reference unavailable on this box)"},
+            "config": {"workload": workload_name(a)},
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": orc.num_threads(), "kind": "port",
-                             "sample": f"per step: same scene, {w}x{h}, {spp} spp, depth {a.depth}; BVH build {build_s:.1f} s outside steps"},
+                             "sample": f"CPU oracle port (the OptiX reference is unavailable on this box), {orc.num_threads()} OpenMP threads; "
+                                       f"per step: same scene, {w}x{h}, {spp} spp, depth {a.depth} ({segs // max(1, a.steps)} segments); "
+                                       f"BVH build {build_s:.1f} s outside steps"},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -240,6 +269,40 @@ class InputPipeline:
         self.torch.cuda.current_stream().wait_stream(self.copy_stream)
 
 
+def build_100m(pkg, synth, torch, dev, ctx, stream, peak, n_target=100_000_000, steps=3):
+    """The LBVH-build half of BASELINE.json's metric at the C5 size: a 10^8-sphere jittered-HCP packing generated on
+    the device, then per step the reference's per-frame particle update (rt_spheres_advect) and a full rebuild
+    (rt_accel_build).  Build time = CUDA events inside rt_accel_build (rt_stats.build_ms), median of `steps`."""
+    base_c, base_r, vel = synth.hcp_spheres_device(torch, n_target, dev)
+    n = int(base_r.numel())
+    d_c, d_r = torch.empty_like(base_c), torch.empty_like(base_r)
+    grey = np.float32([[0.6, 0.6, 0.6]])
+    sc = pkg.Scene(ctx)
+    sc.set_materials(grey.ctypes.data, 1, None, 0)
+    g = sc.add_spheres(d_c.data_ptr(), d_r.data_ptr(), n)
+    sc.add_instance(g, None, pkg.RT_MAT_ROUGH, 0, 0)
+    ms, adv = [], []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for f in range(steps + 1):
+        e0.record()
+        ctx.spheres_advect(base_c.data_ptr(), base_r.data_ptr(), vel.data_ptr(), n, 2.56, 256, f, [0.0, 0.0, 0.0], [1.0, 1.0, 1.0],
+                           d_c.data_ptr(), d_r.data_ptr(), stream)
+        e1.record()
+        sc.build(stream)
+        st = sc.stats()  # synchronises
+        if f:            # the first build allocates
+            ms.append(float(st.build_ms))
+            adv.append(e0.elapsed_time(e1))
+    out = {"n_prims": int(st.n_prims), "ms": float(np.median(ms)), "advect_ms": float(np.median(adv)),
+           "mprims_per_s": int(st.n_prims) / (float(np.median(ms)) * 1e-3) / 1e6, "bytes_per_prim": 224,
+           "hbm_frac": int(st.n_prims) * 224 / (float(np.median(ms)) * 1e-3) / 1e9 / peak, "device_bytes": int(st.device_bytes),
+           "workload": f"C5-size: {n} sphere jittered-HCP packing (phi 0.55) generated on the device; per step rt_spheres_advect + rt_accel_build; median of {steps}"}
+    sc.close()
+    del base_c, base_r, vel, d_c, d_r
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -256,7 +319,7 @@ def run_ours(a):
     assert world_size == a.gpus or world_size == 1 and a.gpus == 1, f"launch with torchrun --nproc-per-node {a.gpus}"
     spp_rank = mg.spp_partition(a.spp, world_size, rank)[1]
 
-    host = build_scene_host(a, pkg, synth)
+    host = build_scene_host(a, synth, lambda cnt: pkg.bake_color_ramp("terrain", cnt))
     cam = pkg.camera_configure(**synth.c4_camera())
     n = a.n_spheres
     npix = a.width * a.height
@@ -287,6 +350,8 @@ def run_ours(a):
     sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
     sc.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
     stream = torch.cuda.current_stream().cuda_stream
+    sc.build(stream)
+    scene_bytes = int(sc.stats().device_bytes)  # primitives + BVH, before any ray queue exists
     xch = None
     if world_size > 1 and a.exchange == "peer":
         try:
@@ -374,10 +439,13 @@ def run_ours(a):
         trace_step = dv["trace_ms"] / a.steps                   # this rank's traversal-kernel time per step
         n_launch = max(1, int(st.trace_launches))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
-        traffic, traffic_src = None, None
-        try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same workload only)
+        traffic, traffic_src, tj, tj_note = None, None, {}, None
+        try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same launch shape only)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_extend_wide"]
-            if a.n_spheres == 10_000_000 and a.width == 3840 and a.height == 2160:
+            tj_note = tj.get("limiters")
+            same_shape = (a.n_spheres == 10_000_000 and a.width == 3840 and a.height == 2160 and a.depth == 5 and not a.batch_spp
+                          and min(a.spp // world_size, 32) == tj.get("spp_in_flight"))
+            if same_shape:
                 traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"] + " (%.0f GB/s of DRAM traffic over that launch: the L2 absorbs the rest)" % tj.get("dram_gbs", 0.0)
         except (OSError, KeyError, ValueError):
             pass
@@ -392,7 +460,7 @@ def run_ours(a):
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
-                       "l2": "inputs larger than L2 (BVH + primitives %.0f MB)" % (st.device_bytes / 1e6),
+                       "l2": "inputs larger than L2 (primitives + BVH %.0f MB; with ray queues / path state %.0f MB on the device)" % (scene_bytes / 1e6, st.device_bytes / 1e6),
                        "step": "LBVH rebuild + render + resolve",
                        "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
                                        ("" if world_size == 1 else ("; every rank traces the whole primary pass, counted once in value (replicated copies: %.1f %% of the traced segments)"
@@ -416,18 +484,68 @@ def run_ours(a):
                          "trace_ms_per_step": trace_step, "trace_share_of_step": trace_step / (dv["ms"] / a.steps)},
             "segments_per_step": seg_step,
         }
+        rl = line["roofline"]
+        # what ncu measured on this kernel (profiles/): DRAM traffic is a few per cent of the algorithmic bytes (the
+        # 126 MB L2 holds the upper tree), the kernel's real ceilings are the L1 LSU data pipe (one wavefront per
+        # cycle; every lane's node sits in its own 128-byte line) and instruction issue
+        rl["model"] = "SURVEY 8d: one root-to-leaf walk over 64-byte binary nodes + hit primitive + ray state per segment"
+        if traffic:
+            rl["measured_dram_gbs"] = tj.get("dram_gbs")
+            rl["measured_dram_frac_of_peak"] = (tj.get("dram_gbs") or 0.0) / peak
+            rl["traffic_over_algorithmic"] = traffic / max(rl["algorithmic_bytes_per_launch"], 1.0)
+        rl["measured_limiters"] = tj_note
         if world_size == 1 and not a.no_cpu_baseline:
-            cb, _ = cpu_sample(a, pkg, host, cam, a.cpu_seconds)
+            cb, oimg, (cw, ch, cspp) = cpu_sample(a, host, cam, a.cpu_seconds)
             line["cpu_baseline"] = cb
+            # the image the CPU leg just rendered, rendered again by rt_render at the same size / spp / seed:
+            # primary-hit ids and linear radiance sums must be bit-identical
+            pid = torch.zeros(cw * ch, dtype=torch.int32, device=dev)
+            acc2 = torch.zeros((cw * ch, 4), dtype=torch.float32, device=dev)
+            sc.build(stream)
+            sc.render(cam, cw, ch, cspp, a.depth, a.seed, (0.7, 0.8, 0.9), 0, 0, acc2.data_ptr(), None, None, pid.data_ptr(), stream)
+            torch.cuda.synchronize()
+            g_id = pid.cpu().numpy().view(np.uint32)
+            g_acc = acc2.cpu().numpy()
+            line["parity_check"] = {"against": "CPU oracle, same scene", "width": cw, "height": ch, "spp": cspp, "pixels": cw * ch,
+                                    "prim_id_mismatch": int((g_id != oimg["prim_id"]).sum()),
+                                    "accum_mismatch": int((g_acc.view(np.uint32) != oimg["accum"].view(np.uint32)).any(axis=1).sum()),
+                                    "segments_equal": bool(int(sc.stats().segments) == int(oimg["segments"]))}
         else:
             line["cpu_baseline"] = None
-        print(json.dumps(line))
+    if world_size > 1:
+        # correctness of the N-rank frame: one more frame through the exchange, then rank 0 renders the same samples
+        # alone and compares the two RGBA8 frames (partial sums are re-associated: expect <= 1 LSB)
+        fcheck = a.warmup + a.steps
+        frame(fcheck, False)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            multi = (xch.frame if xch is not None else rgba8).clone()
+            sc.build(stream)
+            sc.render(cam, a.width, a.height, a.spp, a.depth, a.seed, (0.7, 0.8, 0.9), fcheck * a.spp, 0, accum.data_ptr(), None, None, None, stream)
+            ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
+            torch.cuda.synchronize()
+            diff = (multi.to(torch.int16) - rgba8.to(torch.int16)).abs()
+            line["parity_check"] = {"against": "the same frame rendered by rank 0 alone", "pixels": npix,
+                                    "rgba8_max_abs_diff": int(diff.max().item()), "rgba8_pixels_differing": int((diff.amax(dim=1) > 0).sum().item())}
+        dist.barrier()
+    if rank == 0:
+        if world_size == 1 and not a.no_build_100m:
+            sc.close()
+            sc = None
+            del accum, rgba8
+            torch.cuda.empty_cache()
+            try:
+                line["build_100m"] = build_100m(pkg, synth, torch, dev, ctx, stream, peak)
+            except Exception as e:  # noqa: BLE001 - the headline number must still be printed
+                line["build_100m"] = {"error": repr(e)}
     if xch is not None:
         xch.close()
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()
-    sc.close()
+    if sc is not None:
+        sc.close()
     ctx.close()
 
 

@@ -132,7 +132,10 @@ int rt_scene_destroy(rt_scene scene);
  * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf of
  * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch; 0 = auto: up to 32 within a third of free memory),
  * "t1" / "t2" / "t3" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
- * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "compat_shading" (bit 0: sphere normals from the OBJECT-space centre
+ * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "fused" (0, default: wavefront form, one closest-hit launch + one
+ * shading launch per bounce over ray queues of 168 bytes per (pixel, sample) in flight; 1: ONE persistent kernel in which a lane follows a
+ * path from its first scatter to its end, no queues: 40 bytes per (pixel, sample), 14 GB instead of 50 GB on the 4K / 10 M-sphere
+ * workload at 0.96 of the throughput; bit-identical images), "chunk_spp" (fused form: samples per work unit), "compat_shading" (bit 0: sphere normals from the OBJECT-space centre
  * and radius as shader/Shader.cu:124-132 does although the hit point is in world space, bit 1: triangle vertex normals not rotated with
  * their instance as Shader.cu:139-142; default 0 = correct world-space shading), "ray_bins" (8 or 24: key of
  * the per-block grouping of scattered rays: octant, or octant x dominant axis), "shade_threads" (512 or

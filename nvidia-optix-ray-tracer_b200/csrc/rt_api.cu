@@ -120,6 +120,8 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     else if (k == "leaf_max") { s.leaf_max = (uint32_t)std::min<int64_t>(8, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(0, value));
     else if (k == "wide") { s.wide = value != 0; s.built = false; }
+    else if (k == "fused") s.fused = value != 0;
+    else if (k == "chunk_spp") s.chunk_spp = (uint32_t)std::min<int64_t>(1024, std::max<int64_t>(1, value));
     else if (k == "compat_shading") { s.compat = (uint32_t)(value & 3); s.built = false; }
     else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "t2") s.t2 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
@@ -147,7 +149,7 @@ int rt_scene_destroy(rt_scene scene) {
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();
     s.wnodes.release(); s.wslot_geom.release(); s.wslot_prim.release(); s.wslot_mat.release();
-    s.phit.release(); s.hit.release(); s.u_skip.release(); s.prim_fetch.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.counters.release(); s.seg_total.release();
+    s.phit.release(); s.hit.release(); s.u_skip.release(); s.prim_fetch.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.hit_pix.release(); s.rng_start.release(); s.rng_pix_off.release(); s.counters.release(); s.seg_total.release();
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);

@@ -392,7 +392,212 @@ __device__ __forceinline__ void fill_perm_table(uint8_t (*s_perm)[256]) {
     __syncthreads();
 }
 
+// ---- per-lane state of one closest-hit query over the 8-wide tree (kept in registers)
+struct WideTrav {
+    uint32_t gbase, gmask, pbase, pmask, pbase2, pmask2;
+    int sp;
+    bool huge_done, huge_wait;
+    float tmin, tmax, a, inv_a, ix, iy, iz, ox, oy, oz;
+    uint32_t oct, skip_slot;
+    Hit best;
+};
+__device__ __forceinline__ void trav_clear(WideTrav &t) {
+    t.gbase = t.gmask = t.pbase = t.pmask = t.pbase2 = t.pmask2 = 0u;
+    t.sp = 0;
+    t.huge_done = true;
+    t.huge_wait = false;
+    t.tmin = RT_ZERO;
+    t.tmax = RT_INF;
+    t.a = t.inv_a = 1.0f;
+    t.ix = t.iy = t.iz = t.ox = t.oy = t.oz = 0.0f;
+    t.oct = 0u;
+    t.skip_slot = kNoSlot;
+    t.best.t = 0.0f;
+    t.best.slot = kNoSlot;
+    t.best.u = t.best.v = 0.0f;
+}
+// origin and direction are NOT kept in registers: the node test only needs 1/d and -o/d, the primitive
+// tests re-read the ray (queue entry: an L1/L2 hit; fused path kernel: shared memory)
+__device__ __forceinline__ void trav_start(WideTrav &t, F3 ro, F3 rd, float tmin, float tmax, uint32_t skip_slot,
+                                           uint32_t n_huge, bool have_tree) {
+    t.tmin = tmin;
+    t.tmax = tmax;
+    t.skip_slot = skip_slot;
+    t.best.t = tmax;
+    t.best.slot = kNoSlot;
+    t.best.u = t.best.v = 0.0f;
+    t.a = dot(rd, rd);
+    t.inv_a = 1.0f / t.a;
+    // reciprocal direction, clamped so that 0 * inf never appears
+    const float ex = fabsf(rd.x) < 1e-30f ? copysignf(1e-30f, rd.x) : rd.x;
+    const float ey = fabsf(rd.y) < 1e-30f ? copysignf(1e-30f, rd.y) : rd.y;
+    const float ez = fabsf(rd.z) < 1e-30f ? copysignf(1e-30f, rd.z) : rd.z;
+    t.ix = 1.0f / ex; t.iy = 1.0f / ey; t.iz = 1.0f / ez;
+    t.ox = -ro.x * t.ix; t.oy = -ro.y * t.iy; t.oz = -ro.z * t.iz;
+    t.oct = (t.ix >= 0.0f ? 1u : 0u) | (t.iy >= 0.0f ? 2u : 0u) | (t.iz >= 0.0f ? 4u : 0u);
+    t.huge_done = n_huge == 0;
+    t.huge_wait = false;
+    t.sp = 0;
+    t.pmask = t.pmask2 = 0;
+    t.gbase = 0;
+    t.gmask = have_tree ? 0x8000u : 0u;  // root: slot 7^oct of an imask-0 group -> index 0
+}
+__device__ __forceinline__ bool trav_has_nodes(const WideTrav &t) { return (t.gmask >> 8) != 0 || t.sp > 0; }
+__device__ __forceinline__ bool trav_wants_node(const WideTrav &t) { return (t.pmask2 >> 16) == 0 && trav_has_nodes(t); }
+__device__ __forceinline__ bool trav_wants_prim(const WideTrav &t) { return (t.pmask >> 16) != 0; }
+__device__ __forceinline__ bool trav_tree_done(const WideTrav &t) { return !trav_has_nodes(t) && (t.pmask >> 16) == 0; }
+
+// One wide-node visit of a lane: pop the next node group entry, fetch the node (five 128-bit loads), slab-test
+// its 8 quantised child boxes, queue the hit internal children (octant order) and the hit leaf primitives.
 // `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
+__device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const float4 *__restrict__ wn, uint32_t magic,
+                                          const uint8_t (*s_perm)[256]) {
+    if ((t.gmask >> 8) == 0) {
+        const uint2 e = stack.pop(--t.sp);
+        t.gbase = e.x;
+        t.gmask = e.y;
+    }
+    const uint32_t bit = 31u - (uint32_t)__clz(t.gmask);
+    t.gmask &= ~(1u << bit);
+    const uint32_t slot = (bit - 8u) ^ t.oct;
+    const uint32_t child = t.gbase + __popc(t.gmask & ((1u << slot) - 1u));
+    if (t.gmask >> 8) stack.push(t.sp++, make_uint2(t.gbase, t.gmask));
+
+    const float4 *q = wn + 5 * (size_t)child;
+    const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
+    const uint32_t eim = __float_as_uint(w0.w);
+    const float sx = __uint_as_float((eim & 0xFFu) << 23) * t.ix;
+    const float sy = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * t.iy;
+    const float sz = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * t.iz;
+    // t = (2^23 + q) * s + (b - 2^23 * s), b = (origin - o) / d
+    const float bx = __fmaf_rn(-8388608.0f, sx, __fmaf_rn(w0.x, t.ix, t.ox));
+    const float by = __fmaf_rn(-8388608.0f, sy, __fmaf_rn(w0.y, t.iy, t.oy));
+    const float bz = __fmaf_rn(-8388608.0f, sz, __fmaf_rn(w0.z, t.iz, t.oz));
+    const unsigned long long sx2 = pack2(sx, sx), sy2 = pack2(sy, sy), sz2 = pack2(sz, sz);
+    const unsigned long long bx2 = pack2(bx, bx), by2 = pack2(by, by), bz2 = pack2(bz, bz);
+    const bool px = t.ix >= 0.0f, py = t.iy >= 0.0f, pz = t.iz >= 0.0f;
+    uint32_t hm = 0;  // bit j = child slot j hit
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const uint32_t lox = __float_as_uint(h ? w2.y : w2.x), loy = __float_as_uint(h ? w2.w : w2.z);
+        const uint32_t loz = __float_as_uint(h ? w3.y : w3.x), hix = __float_as_uint(h ? w3.w : w3.z);
+        const uint32_t hiy = __float_as_uint(h ? w4.y : w4.x), hiz = __float_as_uint(h ? w4.w : w4.z);
+        const uint32_t nx = px ? lox : hix, fx = px ? hix : lox;
+        const uint32_t ny = py ? loy : hiy, fy = py ? hiy : loy;
+        const uint32_t nz = pz ? loz : hiz, fz = pz ? hiz : loz;
+#pragma unroll
+        for (int jp = 0; jp < 2; jp++) {
+            float tnx[2], tfx[2], tny[2], tfy[2], tnz[2], tfz[2];
+            if (jp == 0) {
+                ffma2(tnx[0], tnx[1], qfloat<0>(nx, magic), qfloat<1>(nx, magic), sx2, bx2);
+                ffma2(tfx[0], tfx[1], qfloat<0>(fx, magic), qfloat<1>(fx, magic), sx2, bx2);
+                ffma2(tny[0], tny[1], qfloat<0>(ny, magic), qfloat<1>(ny, magic), sy2, by2);
+                ffma2(tfy[0], tfy[1], qfloat<0>(fy, magic), qfloat<1>(fy, magic), sy2, by2);
+                ffma2(tnz[0], tnz[1], qfloat<0>(nz, magic), qfloat<1>(nz, magic), sz2, bz2);
+                ffma2(tfz[0], tfz[1], qfloat<0>(fz, magic), qfloat<1>(fz, magic), sz2, bz2);
+            } else {
+                ffma2(tnx[0], tnx[1], qfloat<2>(nx, magic), qfloat<3>(nx, magic), sx2, bx2);
+                ffma2(tfx[0], tfx[1], qfloat<2>(fx, magic), qfloat<3>(fx, magic), sx2, bx2);
+                ffma2(tny[0], tny[1], qfloat<2>(ny, magic), qfloat<3>(ny, magic), sy2, by2);
+                ffma2(tfy[0], tfy[1], qfloat<2>(fy, magic), qfloat<3>(fy, magic), sy2, by2);
+                ffma2(tnz[0], tnz[1], qfloat<2>(nz, magic), qfloat<3>(nz, magic), sz2, bz2);
+                ffma2(tfz[0], tfz[1], qfloat<2>(fz, magic), qfloat<3>(fz, magic), sz2, bz2);
+            }
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], t.tmin));
+                const float thi = fminf(fminf(tfx[e], tfy[e]), fminf(tfz[e], t.best.t));
+                if (tlo <= thi * 1.000002f) hm |= 1u << (4 * h + 2 * jp + e);  // empty slots hold an inverted box
+            }
+        }
+    }
+    const uint32_t imask = eim >> 24, leafmask = __float_as_uint(w1.z) & 0xFFu;
+    t.gbase = __float_as_uint(w1.x);
+    t.gmask = imask | ((uint32_t)s_perm[t.oct][hm & imask] << 8);
+    const uint32_t pm = hm & leafmask;
+    if (pm) {
+        if ((t.pmask >> 16) == 0) {
+            t.pbase = __float_as_uint(w1.y);
+            t.pmask = leafmask | (pm << 16);
+        } else {
+            t.pbase2 = __float_as_uint(w1.y);
+            t.pmask2 = leafmask | (pm << 16);
+        }
+    }
+}
+
+// One postponed primitive test of a lane (ray origin / direction supplied by the caller).
+__device__ __forceinline__ void trav_prim(WideTrav &t, const SceneDev &sc, F3 ro, F3 rd) {
+    const uint32_t b = (uint32_t)__ffs(t.pmask >> 16) - 1u;
+    t.pmask &= ~(0x10000u << b);
+    Ray r;
+    r.o = ro;
+    r.d = rd;
+    r.tmin = t.tmin;
+    r.tmax = t.tmax;
+    test_slot(sc, r, t.a, t.inv_a, t.pbase + __popc(t.pmask & ((1u << b) - 1u)), t.skip_slot, t.best);
+    if ((t.pmask >> 16) == 0 && (t.pmask2 >> 16) != 0) {
+        t.pbase = t.pbase2;
+        t.pmask = t.pmask2;
+        t.pmask2 = 0;
+    }
+}
+
+// Rays whose tree walk is over: outlier primitives (BuildInfo.huge_*).  A segment with both ends inside the
+// outlier-free box is done at once; the others wait (huge_wait) until at least t3 lanes of the warp are in the
+// same state or nothing else is left to do, then cull the outliers by their boxes against the closest hit so
+// far and queue the survivors for the primitive phase.  WARP-COLLECTIVE: every lane must call it; `alive` =
+// the lane holds a ray, (ro, rd) its origin and direction (read only when the tree walk has just ended).
+__device__ __forceinline__ void trav_outliers(WideTrav &t, bool alive, const BuildInfo *__restrict__ info, uint32_t n_huge,
+                                              int t3, F3 ro, F3 rd) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    if (alive && !t.huge_done && !t.huge_wait && trav_tree_done(t)) {
+        bool need = t.best.slot == kNoSlot;
+        if (!need) {
+            const float ex = ro.x + t.best.t * rd.x, ey = ro.y + t.best.t * rd.y, ez = ro.z + t.best.t * rd.z;
+            const float l0 = info->free_lo[0], l1 = info->free_lo[1], l2 = info->free_lo[2];
+            const float h0 = info->free_hi[0], h1 = info->free_hi[1], h2 = info->free_hi[2];
+            const bool in_o = ro.x > l0 && ro.x < h0 && ro.y > l1 && ro.y < h1 && ro.z > l2 && ro.z < h2;
+            const bool in_e = ex > l0 && ex < h0 && ey > l1 && ey < h1 && ez > l2 && ez < h2;
+            need = !(in_o && in_e);
+        }
+        t.huge_wait = need;
+        t.huge_done = !need;
+    }
+    const uint32_t m3 = __ballot_sync(FULL, alive && t.huge_wait);
+    if (m3 && (__popc(m3) >= t3 || !__any_sync(FULL, alive && !t.huge_wait && !trav_tree_done(t)))) {
+        // warp-cooperative cull: the waiting rays take turns, lane k tests outlier box k
+        uint32_t mine = 0;
+        float hl0 = 0, hl1 = 0, hl2 = 0, hh0 = 0, hh1 = 0, hh2 = 0;
+        if (lane < n_huge) {
+            hl0 = info->huge_lo[lane][0]; hl1 = info->huge_lo[lane][1]; hl2 = info->huge_lo[lane][2];
+            hh0 = info->huge_hi[lane][0]; hh1 = info->huge_hi[lane][1]; hh2 = info->huge_hi[lane][2];
+        }
+        for (uint32_t rem = m3; rem; rem &= rem - 1u) {
+            const int src = __ffs(rem) - 1;
+            const float rix = __shfl_sync(FULL, t.ix, src), riy = __shfl_sync(FULL, t.iy, src), riz = __shfl_sync(FULL, t.iz, src);
+            const float rox = __shfl_sync(FULL, t.ox, src), roy = __shfl_sync(FULL, t.oy, src), roz = __shfl_sync(FULL, t.oz, src);
+            const float rt0 = __shfl_sync(FULL, t.tmin, src), rt1 = __shfl_sync(FULL, t.best.t, src);
+            const float x0 = __fmaf_rn(hl0, rix, rox), x1 = __fmaf_rn(hh0, rix, rox);
+            const float y0 = __fmaf_rn(hl1, riy, roy), y1 = __fmaf_rn(hh1, riy, roy);
+            const float z0 = __fmaf_rn(hl2, riz, roz), z1 = __fmaf_rn(hh2, riz, roz);
+            const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), rt0));
+            const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), rt1));
+            const uint32_t mm = __ballot_sync(FULL, lane < n_huge && tlo <= thi * 1.000002f);
+            if ((int)lane == src) mine = mm;
+        }
+        if (alive && t.huge_wait) {
+            t.pbase = info->huge_slot[0];
+            t.pmask = 0xFFFFu | (mine << 16);  // all kMaxHuge <= 16 slots present: primitive k = pbase + k
+            t.huge_wait = false;
+            t.huge_done = true;
+        }
+    }
+}
+__device__ __forceinline__ bool trav_finished(const WideTrav &t) { return t.huge_done && trav_tree_done(t); }
+
+// Closest hit for a buffer of rays (wavefront form): persistent warps, dynamic ray fetch.
 __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
                                                  float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic,
                                                  const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS]) {
@@ -406,18 +611,9 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
 
     WideStack stack;
     stack.sh = s_stack;
-    int sp = 0;
-    uint32_t gbase = 0, gmask = 0, pbase = 0, pmask = 0, pbase2 = 0, pmask2 = 0;
-    bool huge_done = true, huge_wait = false;
-    uint32_t idx = 0, skip_slot = kNoSlot, oct = 0;
-    // origin and direction are NOT kept in registers: the node test only needs 1/d and -o/d, the
-    // primitive tests re-read the ray from the queue (an L1/L2 hit), which keeps the kernel at 64 registers
-    float tmin = RT_ZERO, tmax = RT_INF;
-    Hit best;
-    best.t = 0.0f;
-    best.slot = kNoSlot;
-    best.u = best.v = 0.0f;
-    float a = 1.0f, inv_a = 1.0f, ix = 0, iy = 0, iz = 0, ox = 0, oy = 0, oz = 0;
+    WideTrav t;
+    trav_clear(t);
+    uint32_t idx = 0;
     bool alive = false, exhausted = false;
 
     for (;;) {
@@ -432,33 +628,9 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
             if (!alive && i < n) {
                 const float4 o4 = in.o[i], d4 = in.d[i];
                 idx = i;
-                const F3 rd = f3(d4.x, d4.y, d4.z);
-                if (in.skip) {
-                    tmin = o4.w;
-                    tmax = d4.w;
-                    skip_slot = in.skip[i];
-                } else {
-                    tmin = RT_ZERO;  // Shader.cu:231-233, 264-267
-                    tmax = RT_INF;
-                    skip_slot = __float_as_uint(d4.w);
-                }
-                best.t = tmax;
-                best.slot = kNoSlot;
-                best.u = best.v = 0.0f;
-                a = dot(rd, rd);
-                inv_a = 1.0f / a;
-                const float ex = fabsf(rd.x) < 1e-30f ? copysignf(1e-30f, rd.x) : rd.x;
-                const float ey = fabsf(rd.y) < 1e-30f ? copysignf(1e-30f, rd.y) : rd.y;
-                const float ez = fabsf(rd.z) < 1e-30f ? copysignf(1e-30f, rd.z) : rd.z;
-                ix = 1.0f / ex; iy = 1.0f / ey; iz = 1.0f / ez;
-                ox = -o4.x * ix; oy = -o4.y * iy; oz = -o4.z * iz;
-                oct = (ix >= 0.0f ? 1u : 0u) | (iy >= 0.0f ? 2u : 0u) | (iz >= 0.0f ? 4u : 0u);
-                huge_done = n_huge == 0;
-                huge_wait = false;
-                sp = 0;
-                pmask = pmask2 = 0;
-                gbase = 0;
-                gmask = have_tree ? 0x8000u : 0u;  // root: slot 7^oct of an imask-0 group -> index 0
+                // path queue: Shader.cu:231-233, 264-267 (tmin 1e-6, tmax 1e16); user rays carry their own range
+                trav_start(t, f3(o4.x, o4.y, o4.z), f3(d4.x, d4.y, d4.z), in.skip ? o4.w : RT_ZERO, in.skip ? d4.w : RT_INF,
+                           in.skip ? in.skip[i] : __float_as_uint(d4.w), n_huge, have_tree);
                 alive = true;
             }
         }
@@ -467,168 +639,41 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
         // ---- phase 1: wide nodes
         bool first = true;
         for (;;) {
-            const bool want = alive && (pmask2 >> 16) == 0 && ((gmask >> 8) != 0 || sp > 0);
+            const bool want = alive && trav_wants_node(t);
             const uint32_t mw = __ballot_sync(FULL, want);
             if (!mw) break;
-            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && (pmask >> 16) != 0)) break;
+            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && trav_wants_prim(t))) break;
             first = false;
-            if (want) {
-                if ((gmask >> 8) == 0) {
-                    const uint2 e = stack.pop(--sp);
-                    gbase = e.x;
-                    gmask = e.y;
-                }
-                const uint32_t bit = 31u - (uint32_t)__clz(gmask);
-                gmask &= ~(1u << bit);
-                const uint32_t slot = (bit - 8u) ^ oct;
-                const uint32_t child = gbase + __popc(gmask & ((1u << slot) - 1u));
-                if (gmask >> 8) stack.push(sp++, make_uint2(gbase, gmask));
-
-                const float4 *q = wn + 5 * (size_t)child;
-                const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
-                const uint32_t eim = __float_as_uint(w0.w);
-                const float sx = __uint_as_float((eim & 0xFFu) << 23) * ix;
-                const float sy = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * iy;
-                const float sz = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * iz;
-                // t = (2^23 + q) * s + (b - 2^23 * s), b = (origin - o) / d
-                const float bx = __fmaf_rn(-8388608.0f, sx, __fmaf_rn(w0.x, ix, ox));
-                const float by = __fmaf_rn(-8388608.0f, sy, __fmaf_rn(w0.y, iy, oy));
-                const float bz = __fmaf_rn(-8388608.0f, sz, __fmaf_rn(w0.z, iz, oz));
-                const unsigned long long sx2 = pack2(sx, sx), sy2 = pack2(sy, sy), sz2 = pack2(sz, sz);
-                const unsigned long long bx2 = pack2(bx, bx), by2 = pack2(by, by), bz2 = pack2(bz, bz);
-                const bool px = ix >= 0.0f, py = iy >= 0.0f, pz = iz >= 0.0f;
-                uint32_t hm = 0;  // bit j = child slot j hit
-#pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const uint32_t lox = __float_as_uint(h ? w2.y : w2.x), loy = __float_as_uint(h ? w2.w : w2.z);
-                    const uint32_t loz = __float_as_uint(h ? w3.y : w3.x), hix = __float_as_uint(h ? w3.w : w3.z);
-                    const uint32_t hiy = __float_as_uint(h ? w4.y : w4.x), hiz = __float_as_uint(h ? w4.w : w4.z);
-                    const uint32_t nx = px ? lox : hix, fx = px ? hix : lox;
-                    const uint32_t ny = py ? loy : hiy, fy = py ? hiy : loy;
-                    const uint32_t nz = pz ? loz : hiz, fz = pz ? hiz : loz;
-#pragma unroll
-                    for (int jp = 0; jp < 2; jp++) {
-                        float tnx[2], tfx[2], tny[2], tfy[2], tnz[2], tfz[2];
-                        if (jp == 0) {
-                            ffma2(tnx[0], tnx[1], qfloat<0>(nx, magic), qfloat<1>(nx, magic), sx2, bx2);
-                            ffma2(tfx[0], tfx[1], qfloat<0>(fx, magic), qfloat<1>(fx, magic), sx2, bx2);
-                            ffma2(tny[0], tny[1], qfloat<0>(ny, magic), qfloat<1>(ny, magic), sy2, by2);
-                            ffma2(tfy[0], tfy[1], qfloat<0>(fy, magic), qfloat<1>(fy, magic), sy2, by2);
-                            ffma2(tnz[0], tnz[1], qfloat<0>(nz, magic), qfloat<1>(nz, magic), sz2, bz2);
-                            ffma2(tfz[0], tfz[1], qfloat<0>(fz, magic), qfloat<1>(fz, magic), sz2, bz2);
-                        } else {
-                            ffma2(tnx[0], tnx[1], qfloat<2>(nx, magic), qfloat<3>(nx, magic), sx2, bx2);
-                            ffma2(tfx[0], tfx[1], qfloat<2>(fx, magic), qfloat<3>(fx, magic), sx2, bx2);
-                            ffma2(tny[0], tny[1], qfloat<2>(ny, magic), qfloat<3>(ny, magic), sy2, by2);
-                            ffma2(tfy[0], tfy[1], qfloat<2>(fy, magic), qfloat<3>(fy, magic), sy2, by2);
-                            ffma2(tnz[0], tnz[1], qfloat<2>(nz, magic), qfloat<3>(nz, magic), sz2, bz2);
-                            ffma2(tfz[0], tfz[1], qfloat<2>(fz, magic), qfloat<3>(fz, magic), sz2, bz2);
-                        }
-#pragma unroll
-                        for (int e = 0; e < 2; e++) {
-                            const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], tmin));
-                            const float thi = fminf(fminf(tfx[e], tfy[e]), fminf(tfz[e], best.t));
-                            if (tlo <= thi * 1.000002f) hm |= 1u << (4 * h + 2 * jp + e);  // empty slots hold an inverted box
-                        }
-                    }
-                }
-                const uint32_t imask = eim >> 24, leafmask = __float_as_uint(w1.z) & 0xFFu;
-                gbase = __float_as_uint(w1.x);
-                gmask = imask | ((uint32_t)s_perm[oct][hm & imask] << 8);
-                const uint32_t pm = hm & leafmask;
-                if (pm) {
-                    if ((pmask >> 16) == 0) {
-                        pbase = __float_as_uint(w1.y);
-                        pmask = leafmask | (pm << 16);
-                    } else {
-                        pbase2 = __float_as_uint(w1.y);
-                        pmask2 = leafmask | (pm << 16);
-                    }
-                }
-            }
+            if (want) trav_node(t, stack, wn, magic, s_perm);
         }
 
         // ---- phase 2: postponed primitives, one per iteration
         first = true;
         for (;;) {
-            const bool hl = alive && (pmask >> 16) != 0;
+            const bool hl = alive && trav_wants_prim(t);
             const uint32_t ml = __ballot_sync(FULL, hl);
             if (!ml) break;
-            if (!first && __popc(ml) < t2 &&
-                __any_sync(FULL, alive && (pmask2 >> 16) == 0 && ((gmask >> 8) != 0 || sp > 0)))
-                break;
+            if (!first && __popc(ml) < t2 && __any_sync(FULL, alive && trav_wants_node(t))) break;
             first = false;
             if (hl) {
-                const uint32_t b = (uint32_t)__ffs(pmask >> 16) - 1u;
-                pmask &= ~(0x10000u << b);
                 const float4 o4 = in.o[idx], d4 = in.d[idx];
-                Ray r;
-                r.o = f3(o4.x, o4.y, o4.z);
-                r.d = f3(d4.x, d4.y, d4.z);
-                r.tmin = tmin;
-                r.tmax = tmax;
-                test_slot(sc, r, a, inv_a, pbase + __popc(pmask & ((1u << b) - 1u)), skip_slot, best);
-                if ((pmask >> 16) == 0 && (pmask2 >> 16) != 0) {
-                    pbase = pbase2;
-                    pmask = pmask2;
-                    pmask2 = 0;
-                }
+                trav_prim(t, sc, f3(o4.x, o4.y, o4.z), f3(d4.x, d4.y, d4.z));
             }
         }
 
-        // ---- rays whose tree walk is over: outlier primitives (BuildInfo.huge_*).  A segment with both
-        //      ends inside the outlier-free box is done at once; the others wait (huge_wait) until at least
-        //      t3 lanes of the warp are in the same state or nothing else is left to do, then cull the
-        //      outliers by their boxes against the closest hit so far and queue the survivors for phase 2.
-        if (alive && !huge_done && !huge_wait && (gmask >> 8) == 0 && sp == 0 && (pmask >> 16) == 0) {
-            bool need = best.slot == kNoSlot;
-            if (!need) {
-                const float4 o4 = in.o[idx], d4 = in.d[idx];
-                const float ex = o4.x + best.t * d4.x, ey = o4.y + best.t * d4.y, ez = o4.z + best.t * d4.z;
-                const float l0 = info->free_lo[0], l1 = info->free_lo[1], l2 = info->free_lo[2];
-                const float h0 = info->free_hi[0], h1 = info->free_hi[1], h2 = info->free_hi[2];
-                const bool in_o = o4.x > l0 && o4.x < h0 && o4.y > l1 && o4.y < h1 && o4.z > l2 && o4.z < h2;
-                const bool in_e = ex > l0 && ex < h0 && ey > l1 && ey < h1 && ez > l2 && ez < h2;
-                need = !(in_o && in_e);
-            }
-            huge_wait = need;
-            huge_done = !need;
-        }
+        // ---- outlier primitives
         {
-            const uint32_t m3 = __ballot_sync(FULL, alive && huge_wait);
-            if (m3 && (__popc(m3) >= t3 ||
-                       !__any_sync(FULL, alive && !huge_wait && ((gmask >> 8) != 0 || sp > 0 || (pmask >> 16) != 0)))) {
-                // warp-cooperative cull: the waiting rays take turns, lane k tests outlier box k
-                uint32_t mine = 0;
-                float hl0 = 0, hl1 = 0, hl2 = 0, hh0 = 0, hh1 = 0, hh2 = 0;
-                if (lane < n_huge) {
-                    hl0 = info->huge_lo[lane][0]; hl1 = info->huge_lo[lane][1]; hl2 = info->huge_lo[lane][2];
-                    hh0 = info->huge_hi[lane][0]; hh1 = info->huge_hi[lane][1]; hh2 = info->huge_hi[lane][2];
-                }
-                for (uint32_t rem = m3; rem; rem &= rem - 1u) {
-                    const int src = __ffs(rem) - 1;
-                    const float rix = __shfl_sync(FULL, ix, src), riy = __shfl_sync(FULL, iy, src), riz = __shfl_sync(FULL, iz, src);
-                    const float rox = __shfl_sync(FULL, ox, src), roy = __shfl_sync(FULL, oy, src), roz = __shfl_sync(FULL, oz, src);
-                    const float rt0 = __shfl_sync(FULL, tmin, src), rt1 = __shfl_sync(FULL, best.t, src);
-                    const float x0 = __fmaf_rn(hl0, rix, rox), x1 = __fmaf_rn(hh0, rix, rox);
-                    const float y0 = __fmaf_rn(hl1, riy, roy), y1 = __fmaf_rn(hh1, riy, roy);
-                    const float z0 = __fmaf_rn(hl2, riz, roz), z1 = __fmaf_rn(hh2, riz, roz);
-                    const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), rt0));
-                    const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), rt1));
-                    const uint32_t mm = __ballot_sync(FULL, lane < n_huge && tlo <= thi * 1.000002f);
-                    if ((int)lane == src) mine = mm;
-                }
-                if (alive && huge_wait) {
-                    pbase = info->huge_slot[0];
-                    pmask = 0xFFFFu | (mine << 16);  // all kMaxHuge <= 16 slots present: primitive k = pbase + k
-                    huge_wait = false;
-                    huge_done = true;
-                }
+            F3 ro = f3(0, 0, 0), rd = f3(0, 0, 0);
+            if (alive && !t.huge_done && !t.huge_wait && trav_tree_done(t) && t.best.slot != kNoSlot) {
+                const float4 o4 = in.o[idx], d4 = in.d[idx];
+                ro = f3(o4.x, o4.y, o4.z);
+                rd = f3(d4.x, d4.y, d4.z);
             }
+            trav_outliers(t, alive, info, n_huge, t3, ro, rd);
         }
         // ---- retire finished rays
-        if (alive && huge_done && (gmask >> 8) == 0 && sp == 0 && (pmask >> 16) == 0) {
-            hits[idx] = make_float4(best.slot == kNoSlot ? RT_INF : best.t, __uint_as_float(best.slot), best.u, best.v);
+        if (alive && trav_finished(t)) {
+            hits[idx] = make_float4(t.best.slot == kNoSlot ? RT_INF : t.best.t, __uint_as_float(t.best.slot), t.best.u, t.best.v);
             alive = false;
         }
     }

@@ -200,6 +200,12 @@ struct Scene {
     DevBuf<uint32_t> q_r4[2];
     DevBuf<uint4> q_m[2];         // RT_FLAG_REF_MUL_ON_RETURN only: material words of the path's bounces 1..4
     DevBuf<float4> result;        // per path
+    DevBuf<uint32_t> hit_pix;     // fused form: pixels whose primary ray hit something
+    DevBuf<uint32_t> rng_start;   // fused form: [sample][6][npix] XORWOW state of stream(p, s) per hit pixel
+    DevBuf<uint32_t> rng_pix_off; // fused form: sample offset the state of pixel p in rng_cur stands at (lazy stepping)
+    bool rng_lazy = false;        // rng_cur / rng_off were last written by the fused form
+    bool fused = false;           // option "fused": one persistent path kernel instead of per-bounce wavefront launches
+    uint32_t chunk_spp = 16;      // option "chunk_spp": samples per work unit of the fused kernel
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)
     const float4 *ext_phit = nullptr;  // caller-supplied primary hit records (rt_scene_set_primary_hits)
     DevBuf<uint32_t> prim_fetch;        // fetch counter of rt_render_primary

@@ -437,6 +437,319 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
     }
 }
 
+// ==================================================================== fused path kernel (option "fused", default)
+// The reference's recursion (optixTrace inside closest-hit, Shader.cu:229-241) as ONE persistent kernel: a lane
+// owns a path from its first scatter to its end — closest hit over the 8-wide tree, then the closest-hit / miss
+// program, then the next segment — so no ray queues, no hit records and no per-bounce launches (and drains of
+// the persistent grid) exist: the wavefront form above moves ~200 bytes per segment through HBM and spends 17 %
+// of a C4 frame outside the traversal kernel.  What stays of the wavefront design is the warp-phased traversal
+// (extend_warp_wide): lanes of a warp run wide-node tests, primitive tests and the shading step as three
+// warp-uniform phases, and a lane that has finished a path takes the next work unit from a global counter.
+//
+// Work unit = (hit pixel i, chunk c of kChunk consecutive samples): the unit's samples are traced one after the
+// other by the same lane (the primary hit is shared, Shader.cu:249-261 has no jitter), each with its own XORWOW
+// stream(p, s); k_prepare stores the stream state at the start of every chunk.  Radiance goes to
+// result[i * S + s] and is summed per pixel in sample order by k_accumulate_hits, so the frame is bit-identical
+// to the wavefront form and to the oracle whatever the scheduling.
+// Per-lane path state that is not needed during traversal lives in shared memory ([word][thread]).
+enum PathWord { PW_OX, PW_OY, PW_OZ, PW_DX, PW_DY, PW_DZ, PW_TR, PW_TG, PW_TB, PW_RD, PW_R0, PW_R1, PW_R2, PW_R3, PW_R4,
+                PW_PX, PW_PY, PW_PZ, PW_PIX, PW_IDX, PW_S, PW_SEND, PW_DEPTH, PW_M0, PW_M1, PW_M2, PW_M3, PW_COUNT };
+constexpr int kPathWords = PW_M0;          // words per lane without the reference-order albedo list
+constexpr int kPathWordsRef = PW_COUNT;    // with it (RT_FLAG_REF_MUL_ON_RETURN)
+
+struct PathArgs {
+    CamDev cam;
+    uint32_t W, H, S, chunk, n_chunks, max_depth, flags;
+    F3 bg;
+    const float4 *phit;           // primary hit per pixel
+    const uint32_t *hit_pix;      // compacted list of pixels whose primary ray hit something
+    const uint32_t *n_hit;        // its length (device)
+    const uint32_t *rng_start;    // [S][6][cap]: XORWOW state of stream(p, s) for hit pixel i (written by k_prepare)
+    uint32_t cap;                 // stride of rng_start (= W*H)
+    float4 *result;               // [i * S + s]
+    uint32_t *unit_ctr;           // work-unit counter
+    uint32_t *seg_ctr;            // segments traced by this launch
+};
+
+template <bool kRefMul>
+__device__ __forceinline__ void path_warp(const SceneDev &sc, const PathArgs &a, int t1, int t2, int t3, int fetch_min, uint32_t magic,
+                                          const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS],
+                                          uint32_t (*s_w)[RT_EXTEND_THREADS]) {
+    const uint32_t FULL = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u, tx = threadIdx.x;
+    const uint32_t lt = (1u << lane) - 1u;
+    const float4 *wn = reinterpret_cast<const float4 *>(sc.wnodes);
+    const BuildInfo *info = sc.info;
+    const uint32_t n_huge = info->n_huge;
+    const bool have_tree = info->n_bvh != 0;
+    const uint32_t n_hit = *a.n_hit;
+    const uint32_t n_units = n_hit * a.n_chunks;  // host guarantees npix * n_chunks < 2^32
+
+    WideStack stack;
+    stack.sh = s_stack;
+    WideTrav t;
+    trav_clear(t);
+    bool alive = false;      // the lane holds a ray whose closest hit is being searched
+    bool have_unit = false;  // the lane owns a work unit
+    bool exhausted = false;  // the unit counter has run out (warp-uniform)
+    uint32_t nseg = 0;
+
+#define PWF(k) __uint_as_float(s_w[k][tx])
+    for (;;) {
+        // ---- phase 0: lanes whose ray is finished (or that own nothing) run the closest-hit / miss program,
+        //      start the next sample or fetch the next unit.  Entered when at least fetch_min lanes wait, or
+        //      when nobody has traversal work left.
+        const bool fin = alive && trav_finished(t);
+        const bool idle = !alive && !have_unit && !exhausted;
+        const uint32_t m0 = __ballot_sync(FULL, fin || idle);
+        if (m0 && (__popc(m0) >= fetch_min || !__any_sync(FULL, alive && !fin))) {
+            bool scatter_now = false, start_sample = false;
+            Ray ray;
+            Hit hit;
+            F3 thr = f3(1.0f, 1.0f, 1.0f);
+            Rng r;
+            uint32_t depth = 0;
+            if (fin) {
+                alive = false;
+                depth = s_w[PW_DEPTH][tx];
+                bool path_done = false;
+                F3 rgb = f3(0.0f, 0.0f, 0.0f);
+                if (t.best.slot == kNoSlot) {  // __miss__missProgram, Shader.cu:276-287
+                    if (kRefMul) {
+                        rgb = unwind_product(sc, a.bg, make_uint4(s_w[PW_M0][tx], s_w[PW_M1][tx], s_w[PW_M2][tx], s_w[PW_M3][tx]), depth - 1u);
+                    } else {
+                        rgb = f3(PWF(PW_TR) * a.bg.x, PWF(PW_TG) * a.bg.y, PWF(PW_TB) * a.bg.z);
+                    }
+                    path_done = true;
+                } else if (depth >= a.max_depth) {  // Shader.cu:102-107
+                    path_done = true;
+                } else {
+                    ray.o = f3(PWF(PW_OX), PWF(PW_OY), PWF(PW_OZ));
+                    ray.d = f3(PWF(PW_DX), PWF(PW_DY), PWF(PW_DZ));
+                    ray.tmin = RT_ZERO;
+                    ray.tmax = RT_INF;
+                    hit = t.best;
+                    thr = f3(PWF(PW_TR), PWF(PW_TG), PWF(PW_TB));
+                    scatter_now = true;
+                }
+                if (path_done) {
+                    const uint32_t sidx = s_w[PW_S][tx];
+                    a.result[(size_t)s_w[PW_IDX][tx] * a.S + sidx] = make_float4(rgb.x, rgb.y, rgb.z, 0.0f);
+                    s_w[PW_S][tx] = sidx + 1u;
+                    if (sidx + 1u < s_w[PW_SEND][tx]) start_sample = true; else have_unit = false;
+                }
+            }
+            // ---- unit fetch (warp-aggregated)
+            {
+                const uint32_t want = __ballot_sync(FULL, !alive && !have_unit && !scatter_now && !start_sample);
+                if (want && !exhausted) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(a.unit_ctr, (uint32_t)__popc(want));
+                    base = __shfl_sync(FULL, base, 0);
+                    if (base + __popc(want) >= n_units) exhausted = true;
+                    const uint32_t u = base + __popc(want & lt);
+                    if (((want >> lane) & 1u) && u < n_units) {
+                        const uint32_t c = u / n_hit, i = u - c * n_hit;
+                        const uint32_t p = a.hit_pix[i];
+                        const Ray pr = primary_ray(a.cam, p % a.W, p / a.W, a.W, a.H);  // shared by the unit's samples
+                        s_w[PW_PX][tx] = __float_as_uint(pr.d.x); s_w[PW_PY][tx] = __float_as_uint(pr.d.y); s_w[PW_PZ][tx] = __float_as_uint(pr.d.z);
+                        s_w[PW_PIX][tx] = p;
+                        s_w[PW_IDX][tx] = i;
+                        s_w[PW_S][tx] = c * a.chunk;
+                        s_w[PW_SEND][tx] = min(a.S, (c + 1u) * a.chunk);
+                        have_unit = true;
+                        start_sample = true;
+                    }
+                }
+            }
+            if (start_sample) {
+                // stream(p, s): state written by k_prepare (one 32-draw stride after stream(p, s-1))
+                const uint32_t *rs = a.rng_start + (size_t)s_w[PW_S][tx] * 6u * a.cap + s_w[PW_IDX][tx];
+                r.d = rs[0];
+                r.v0 = rs[1 * (size_t)a.cap]; r.v1 = rs[2 * (size_t)a.cap]; r.v2 = rs[3 * (size_t)a.cap];
+                r.v3 = rs[4 * (size_t)a.cap]; r.v4 = rs[5 * (size_t)a.cap];
+                ray.o = a.cam.c;
+                ray.d = f3(PWF(PW_PX), PWF(PW_PY), PWF(PW_PZ));
+                ray.tmin = RT_ZERO;
+                ray.tmax = RT_INF;
+                const float4 h = a.phit[s_w[PW_PIX][tx]];
+                hit.t = h.x;
+                hit.slot = __float_as_uint(h.y);
+                hit.u = h.z;
+                hit.v = h.w;
+                depth = 1u;
+                thr = f3(1.0f, 1.0f, 1.0f);
+                scatter_now = true;
+            } else if (scatter_now) {
+                r.d = s_w[PW_RD][tx];
+                r.v0 = s_w[PW_R0][tx]; r.v1 = s_w[PW_R1][tx]; r.v2 = s_w[PW_R2][tx]; r.v3 = s_w[PW_R3][tx]; r.v4 = s_w[PW_R4][tx];
+            }
+            if (scatter_now) {  // closesthitImpl, Shader.cu:94-242
+                const Scatter s1 = scatter(sc, ray, hit, r);
+                thr = f3(thr.x * s1.alb.x, thr.y * s1.alb.y, thr.z * s1.alb.z);  // :236-238 (on the way down)
+                s_w[PW_OX][tx] = __float_as_uint(s1.P.x); s_w[PW_OY][tx] = __float_as_uint(s1.P.y); s_w[PW_OZ][tx] = __float_as_uint(s1.P.z);
+                s_w[PW_DX][tx] = __float_as_uint(s1.dir.x); s_w[PW_DY][tx] = __float_as_uint(s1.dir.y); s_w[PW_DZ][tx] = __float_as_uint(s1.dir.z);
+                s_w[PW_TR][tx] = __float_as_uint(thr.x); s_w[PW_TG][tx] = __float_as_uint(thr.y); s_w[PW_TB][tx] = __float_as_uint(thr.z);
+                s_w[PW_RD][tx] = r.d;
+                s_w[PW_R0][tx] = r.v0; s_w[PW_R1][tx] = r.v1; s_w[PW_R2][tx] = r.v2; s_w[PW_R3][tx] = r.v3; s_w[PW_R4][tx] = r.v4;
+                if (kRefMul) s_w[PW_M0 + (depth - 1u)][tx] = s1.mat;  // depth <= 4 here (max_depth <= 5)
+                s_w[PW_DEPTH][tx] = depth + 1u;
+                // Shader.cu:230-233: tmin 1e-6, tmax 1e16; by default the ray skips the primitive it leaves
+                trav_start(t, s1.P, s1.dir, RT_ZERO, RT_INF, (a.flags & RT_FLAG_REF_NO_SELF_SKIP) ? kNoSlot : hit.slot, n_huge, have_tree);
+                alive = true;
+                nseg += 1u;
+            }
+        }
+        if (!__any_sync(FULL, alive)) {
+            if (exhausted) break;
+            continue;
+        }
+
+        // ---- phase 1: wide nodes
+        bool first = true;
+        for (;;) {
+            const bool want = alive && trav_wants_node(t);
+            const uint32_t mw = __ballot_sync(FULL, want);
+            if (!mw) break;
+            if (!first && __popc(mw) < t1 && __any_sync(FULL, alive && trav_wants_prim(t))) break;
+            first = false;
+            if (want) trav_node(t, stack, wn, magic, s_perm);
+        }
+        // ---- phase 2: postponed primitives, one per iteration
+        first = true;
+        for (;;) {
+            const bool hl = alive && trav_wants_prim(t);
+            const uint32_t ml = __ballot_sync(FULL, hl);
+            if (!ml) break;
+            if (!first && __popc(ml) < t2 && __any_sync(FULL, alive && trav_wants_node(t))) break;
+            first = false;
+            if (hl) trav_prim(t, sc, f3(PWF(PW_OX), PWF(PW_OY), PWF(PW_OZ)), f3(PWF(PW_DX), PWF(PW_DY), PWF(PW_DZ)));
+        }
+        // ---- outlier primitives
+        trav_outliers(t, alive, info, n_huge, t3, f3(PWF(PW_OX), PWF(PW_OY), PWF(PW_OZ)), f3(PWF(PW_DX), PWF(PW_DY), PWF(PW_DZ)));
+    }
+#undef PWF
+    // segments traced by this warp
+    for (int o = 16; o > 0; o >>= 1) nseg += __shfl_xor_sync(FULL, nseg, o);
+    if (lane == 0 && nseg) atomicAdd(a.seg_ctr, nseg);
+}
+
+template <int kMinBlocks, bool kRefMul>
+__global__ void __launch_bounds__(RT_EXTEND_THREADS, kMinBlocks)
+k_path(SceneDev sc, PathArgs a, int t1, int t2, int t3, int fetch_min, uint32_t magic) {
+    __shared__ uint8_t s_perm[8][256];
+    __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
+    __shared__ uint32_t s_w[kRefMul ? kPathWordsRef : kPathWords][RT_EXTEND_THREADS];
+    fill_perm_table(s_perm);
+    path_warp<kRefMul>(sc, a, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_w);
+}
+
+// Per pixel, before k_path.  Pixels whose primary ray hit something (and may scatter: max_depth > 1) are appended to
+// hit_pix and get the XORWOW state of each of their S streams, stream(p, s) = curand_init(seed, p, (offset + s) * 32),
+// by stepping the pixel's state (full warps: the hit pixels of an 8x4 tile mostly come together).  All other
+// pixels receive their S samples here (miss: 1 * background, Shader.cu:276-287; depth cut-off: 0, :102-107), added one by
+// one in sample order, and do NOT step their state: rng_off[p] records the sample offset a pixel's state stands
+// at, and a pixel that starts to hit after a rebuild catches up first (or is re-initialised when it lags far).
+// The list order is block-ordered (tile order inside a block): neighbouring lanes of k_path work on neighbouring pixels.
+constexpr int kPrepThreads = 256;
+constexpr uint32_t kRngMaxLag = 2048;  // samples; beyond it curand_init (sequence skip by matrices) is cheaper than stepping
+__global__ void __launch_bounds__(kPrepThreads)
+k_prepare(uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg, const float4 *__restrict__ phit, uint32_t *__restrict__ rng,
+          uint32_t *__restrict__ rng_off, unsigned long long seed, uint32_t sample_offset, uint32_t *__restrict__ hit_pix,
+          uint32_t *__restrict__ n_hit, uint32_t *__restrict__ rng_start, float4 *__restrict__ accum, int fresh) {
+    __shared__ uint32_t s_warp[kPrepThreads / 32];
+    __shared__ uint32_t s_base;
+    uint32_t x, y;
+    const bool valid = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y);
+    const uint32_t npix = W * H;
+    const uint32_t p = valid ? y * W + x : 0u;
+    bool is_hit = false;
+    if (valid) is_hit = __float_as_uint(phit[p].y) != kNoSlot;
+    const bool go = is_hit && max_depth > 1u;
+    // block-ordered append
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, go);
+    if (lane == 0) s_warp[w] = __popc(bal);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+        for (int k = 0; k < kPrepThreads / 32; k++) {
+            const uint32_t c = s_warp[k];
+            s_warp[k] = tot;
+            tot += c;
+        }
+        s_base = tot ? atomicAdd(n_hit, tot) : 0u;
+    }
+    __syncthreads();
+    const uint32_t i = s_base + s_warp[w] + __popc(bal & ((1u << lane) - 1u));
+    if (!valid) return;
+    if (!go) {
+        if (accum) {
+            float4 acc = fresh ? make_float4(0, 0, 0, 0) : accum[p];
+            const float4 add = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
+            for (uint32_t s = 0; s < S; s++) {
+                acc.x += add.x; acc.y += add.y; acc.z += add.z;
+            }
+            acc.w += (float)S;
+            accum[p] = acc;
+        }
+        return;
+    }
+    hit_pix[i] = p;
+    Rng st;
+    const uint32_t have = rng_off[p];
+    if (have > sample_offset || sample_offset - have > kRngMaxLag) {
+        curandStateXORWOW cs;
+        curand_init(seed, (unsigned long long)p, (unsigned long long)sample_offset * RT_RNG_SAMPLE_STRIDE, &cs);
+        st.d = cs.d; st.v0 = cs.v[0]; st.v1 = cs.v[1]; st.v2 = cs.v[2]; st.v3 = cs.v[3]; st.v4 = cs.v[4];
+    } else {
+        st.d = rng[0 * (size_t)npix + p];
+        st.v0 = rng[1 * (size_t)npix + p];
+        st.v1 = rng[2 * (size_t)npix + p];
+        st.v2 = rng[3 * (size_t)npix + p];
+        st.v3 = rng[4 * (size_t)npix + p];
+        st.v4 = rng[5 * (size_t)npix + p];
+        for (uint32_t k = (sample_offset - have) * RT_RNG_SAMPLE_STRIDE; k > 0; k--) (void)rng_next(st);
+    }
+    for (uint32_t s = 0; s < S; s++) {
+        uint32_t *rs = rng_start + (size_t)s * 6u * npix + i;
+        rs[0] = st.d;
+        rs[1 * (size_t)npix] = st.v0;
+        rs[2 * (size_t)npix] = st.v1;
+        rs[3 * (size_t)npix] = st.v2;
+        rs[4 * (size_t)npix] = st.v3;
+        rs[5 * (size_t)npix] = st.v4;
+#pragma unroll 8
+        for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
+    }
+    rng[0 * (size_t)npix + p] = st.d;
+    rng[1 * (size_t)npix + p] = st.v0;
+    rng[2 * (size_t)npix + p] = st.v1;
+    rng[3 * (size_t)npix + p] = st.v2;
+    rng[4 * (size_t)npix + p] = st.v3;
+    rng[5 * (size_t)npix + p] = st.v4;
+    rng_off[p] = sample_offset + S;
+}
+
+// ordered sum of the S path results of every hit pixel (after k_path)
+__global__ void __launch_bounds__(256)
+k_accumulate_hits(const float4 *__restrict__ result, const uint32_t *__restrict__ hit_pix, const uint32_t *__restrict__ n_hit, uint32_t S,
+                  float4 *__restrict__ accum, int fresh) {
+    const uint32_t n = *n_hit;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = hit_pix[i];
+        float4 a = fresh ? make_float4(0, 0, 0, 0) : accum[p];
+        for (uint32_t s = 0; s < S; s++) {
+            const float4 r = result[(size_t)i * S + s];
+            a.x += r.x;
+            a.y += r.y;
+            a.z += r.z;
+        }
+        a.w += (float)S;
+        accum[p] = a;
+    }
+}
+
 // ------------------------------------------------------------------ ordered accumulation of a sample batch
 __global__ void __launch_bounds__(256)
 k_accumulate(const float4 *__restrict__ result, uint32_t S, uint32_t npix, float4 *__restrict__ accum, int fresh) {
@@ -589,7 +902,23 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     // samples per pixel in flight per wavefront batch: larger batches amortise the drain of the persistent
     // traversal grid (C4: 4 -> 32 spp per batch = +5 %); 168 bytes of queue per (pixel, sample).  Auto: up to
     // 32, within a third of the free device memory (and 48 GB).  Results do not depend on it.
+    // Fused form (option "fused", default; needs the 8-wide tree): no queues.  Per batch of Sb samples: 16 bytes of
+    // result and 24 bytes of stream state per (pixel, sample), sized for the worst case (every pixel hits).
+    const bool fused = s->fused && s->wide;
+    const uint32_t chunk = std::max(1u, s->chunk_spp);
     uint32_t Sb = s->batch_spp;
+    if (fused && !Sb) {
+        if (!s->auto_batch || s->auto_batch_npix != npix) {
+            size_t free_b = 0, total_b = 0;
+            RT_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+            const size_t budget = std::min<size_t>((size_t)12 << 30, (free_b + s->bytes) / 4);
+            uint32_t b = 64;
+            while (b > 1 && ((size_t)npix * b * 40 > budget || (uint64_t)npix * b >= (1ull << 32))) b >>= 1;
+            s->auto_batch = b;
+            s->auto_batch_npix = npix;
+        }
+        Sb = s->auto_batch;
+    }
     if (!Sb) {
         if (!s->auto_batch || s->auto_batch_npix != npix) {
             size_t free_b = 0, total_b = 0;
@@ -607,13 +936,19 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     const uint32_t D = fp->max_depth;
 
     RT_CUDA(ctx, s->phit.reserve(npix, &s->bytes));
-    const size_t qn = std::max((size_t)npix, spp ? (size_t)npix * std::min(Sb, spp) : (size_t)0);
+    const size_t qn = fused ? (size_t)npix : std::max((size_t)npix, spp ? (size_t)npix * std::min(Sb, spp) : (size_t)0);
     for (int k = 0; k < 2; k++) {
-        const size_t qk = (k == 0 || spp) ? qn : 1;  // primary rays use queue 0's origin/direction arrays
+        const size_t qk = (k == 0 || (spp && !fused)) ? qn : 1;  // primary rays use queue 0's origin/direction arrays
         RT_CUDA(ctx, s->q_o[k].reserve(qk, &s->bytes));
         RT_CUDA(ctx, s->q_d[k].reserve(qk, &s->bytes));
     }
-    if (spp) {
+    if (spp && fused) {
+        RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
+        RT_CUDA(ctx, s->hit_pix.reserve(npix, &s->bytes));
+        RT_CUDA(ctx, s->rng_pix_off.reserve(npix, &s->bytes));
+        RT_CUDA(ctx, s->rng_start.reserve((size_t)std::min(Sb, spp) * 6 * npix, &s->bytes));
+        RT_CUDA(ctx, s->result.reserve((size_t)npix * std::min(Sb, spp), &s->bytes));
+    } else if (spp) {
         RT_CUDA(ctx, s->rng_base.reserve(6 * (size_t)npix, &s->bytes));
         RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
         for (int k = 0; k < 2; k++) {
@@ -626,8 +961,10 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         RT_CUDA(ctx, s->result.reserve(qn, &s->bytes));
     }
     // counters: [n_batches][D+3] queue sizes, then one fetch counter per k_extend launch
-    const size_t n_cnt = (size_t)(n_batches ? n_batches : 1) * (D + 3);
-    const size_t n_fetch = 1 + (size_t)n_batches * (D + 1);
+    // fused: [n_batches] segment counters (summed by k_tally / rt_get_stats like the queue sizes), then [n_batches]
+    // hit-pixel counts, [n_batches] unit counters and the primary pass's fetch counter
+    const size_t n_cnt = fused ? (size_t)(n_batches ? n_batches : 1) : (size_t)(n_batches ? n_batches : 1) * (D + 3);
+    const size_t n_fetch = fused ? 1 + 2 * (size_t)n_batches : 1 + (size_t)n_batches * (D + 1);
     RT_CUDA(ctx, s->counters.reserve(n_cnt + n_fetch, &s->bytes));
     if (!s->seg_total.p) {
         RT_CUDA(ctx, s->seg_total.reserve(1, &s->bytes));
@@ -638,7 +975,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
 
     RT_CUDA(ctx, cudaEventRecord(s->ev[2], st));
     RT_CUDA(ctx, cudaMemsetAsync(s->counters.p, 0, (n_cnt + n_fetch) * sizeof(uint32_t), st));
-    uint32_t *fetch = s->counters.p + n_cnt;
+    uint32_t *fetch = s->counters.p + n_cnt + (fused ? 2 * (size_t)n_batches : 0);
 
     const SceneDev sd = scene_dev(s);
     CamDev cd;
@@ -654,9 +991,19 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     // (re)positioned (first frame, or a rank of the spp split whose sample blocks are not contiguous from
     // frame to frame) that runs on a side stream next to the primary-visibility pass, which does not need them.
     bool rng_forked = false;
-    if (spp) {
-        const bool base_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
-        const bool cont_ok = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
+    if (spp && fused) {
+        // lazy per-pixel streams (k_prepare): a state is (re)created on demand, so a new seed / size / form only has
+        // to mark every pixel's state as absent
+        const bool ok = s->rng_valid && s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H;
+        if (!ok) {
+            RT_CUDA(ctx, cudaMemsetAsync(s->rng_pix_off.p, 0xFF, (size_t)npix * sizeof(uint32_t), st));
+            s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H;
+            s->rng_valid = true;
+            s->rng_lazy = true;
+        }
+    } else if (spp) {
+        const bool base_ok = s->rng_valid && !s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
+        const bool cont_ok = s->rng_valid && !s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
                              s->rng_cur_off == (uint64_t)fp->sample_offset;
         if (!cont_ok) {
             if (!s->aux_stream) {
@@ -672,6 +1019,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                 s->launches += 1;
                 s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;
                 s->rng_valid = true;
+                s->rng_lazy = false;
             }
             RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s->aux_stream));
             RT_CUDA(ctx, cudaEventRecord(s->ev_join, s->aux_stream));
@@ -699,7 +1047,40 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         s->launches += 1;
     }
 
-    if (spp) {
+    if (spp && fused) {
+        if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
+        const uint32_t grid = (uint32_t)ctx->sm_count * s->extend_blocks_per_sm;
+        uint32_t done = 0;
+        for (uint32_t b = 0; b < n_batches; b++) {
+            const uint32_t S = std::min(Sb, spp - done);
+            const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
+            uint32_t *seg_ctr = s->counters.p + b, *n_hit = s->counters.p + n_cnt + b, *unit_ctr = s->counters.p + n_cnt + n_batches + b;
+            k_prepare<<<div_up(tiles * 32u, kPrepThreads), kPrepThreads, 0, st>>>(W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done,
+                                                                                  s->hit_pix.p, n_hit, s->rng_start.p, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+            s->launches += 1;
+            if (D > 1) {
+                PathArgs pa;
+                pa.cam = cd; pa.W = W; pa.H = H; pa.S = S; pa.chunk = chunk; pa.n_chunks = div_up(S, chunk); pa.max_depth = D; pa.flags = fp->flags;
+                pa.bg = bg; pa.phit = phit; pa.hit_pix = s->hit_pix.p; pa.n_hit = n_hit; pa.rng_start = s->rng_start.p; pa.cap = npix;
+                pa.result = s->result.p; pa.unit_ctr = unit_ctr; pa.seg_ctr = seg_ctr;
+                RT_CUDA(ctx, prof_mark(s, st));
+                const int t1 = (int)s->t1, t2 = (int)s->t2, t3 = (int)s->t3, fm = (int)s->fetch_min;
+                if (ref_mul)
+                    k_path<6, true><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                else if (s->extend_blocks_per_sm >= 8)
+                    k_path<8, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                else if (s->extend_blocks_per_sm == 7)
+                    k_path<7, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                else
+                    k_path<6, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                RT_CUDA(ctx, prof_mark(s, st));
+                k_accumulate_hits<<<(uint32_t)ctx->sm_count * 8u, 256, 0, st>>>(s->result.p, s->hit_pix.p, n_hit, S, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+                s->launches += 2;
+            }
+            done += S;
+        }
+        s->rng_cur_off = (uint64_t)fp->sample_offset + spp;
+    } else if (spp) {
         if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
         const uint32_t shade_grid = (uint32_t)ctx->sm_count * 3u;  // 3 resident blocks of 512 threads (40 registers)
         uint32_t done = 0;

@@ -125,6 +125,47 @@ def hcp_spheres_chunked(n_target: int, phi: float = 0.55, jitter: float = 0.1, s
     return np.ascontiguousarray(out[:n]), np.full(n, r, dtype=np.float32)
 
 
+def hcp_spheres_device(torch, n_target: int, device, phi: float = 0.55, jitter: float = 0.1, seed: int = 0x5EED0005,
+                       chunk_i: int = 32):
+    """The lattice of hcp_spheres generated ON THE DEVICE with torch (C5 is generated on device):
+    same lattice, order and truncation; the +-jitter*r displacement and the fall velocities come from torch's
+    seeded generator instead of SplitMix64 (nothing measured on this scene depends on the jitter values).
+    Returns (centers f32[n,3], radii f32[n], velocities f32[n,3]) as device tensors."""
+    r = (phi * 3.0 / (4.0 * np.pi * n_target)) ** (1.0 / 3.0)
+    a = 2.0 * r * (0.74048 / phi) ** (1.0 / 3.0)
+    nx = int(np.floor((1.0 - 2 * r) / a)) + 1
+    ny = int(np.floor((1.0 - 2 * r) / (a * np.sqrt(3) / 2))) + 1
+    nz = int(np.floor((1.0 - 2 * r) / (a * np.sqrt(6) / 3))) + 1
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    out = torch.empty((n_target, 3), dtype=torch.float32, device=device)
+    lim = 1 - 2 * r
+    n = 0
+    jj = torch.arange(ny, device=device, dtype=torch.float64)
+    kk = torch.arange(nz, device=device, dtype=torch.float64)
+    for i0 in range(0, nx, chunk_i):
+        if n >= n_target:
+            break
+        ii = torch.arange(i0, min(nx, i0 + chunk_i), device=device, dtype=torch.float64)
+        i, j, k = torch.meshgrid(ii, jj, kk, indexing="ij")
+        i, j, k = i.reshape(-1), j.reshape(-1), k.reshape(-1)
+        x = (i + 0.5 * torch.remainder(j + k, 2)) * a
+        y = (j + torch.remainder(k, 2) / 3.0) * (a * np.sqrt(3) / 2)
+        z = k * (a * np.sqrt(6) / 3)
+        keep = (x <= lim) & (y <= lim) & (z <= lim)
+        c = torch.stack([x[keep], y[keep], z[keep]], 1)[: n_target - n]
+        m = len(c)
+        jit = torch.rand((m, 3), generator=gen, device=device, dtype=torch.float32).to(torch.float64)
+        out[n:n + m] = (c + r - 0.5 + (jit * 2.0 - 1.0) * (jitter * r)).to(torch.float32)
+        n += m
+        del i, j, k, x, y, z, keep, c, jit
+    centers = out[:n].contiguous()
+    radii = torch.full((n,), float(np.float32(r)), dtype=torch.float32, device=device)
+    vel = torch.zeros((n, 3), dtype=torch.float32, device=device)
+    vel[:, 2] = -2.0 * (1.0 + 0.1 * torch.rand((n,), generator=gen, device=device, dtype=torch.float32))
+    return centers, radii, vel
+
+
 def dem_velocities(n: int, seed: int = 0x5EED00D5, chunk: int = 1 << 22):
     """C5 analytic motion z(t) = z0 - 2 t (1 + 0.1 hash(id)) as a per-particle velocity (0, 0, vz):
     the frame update is then the reference's Mesh-mode translation (velocity * duration / frames * frame)."""

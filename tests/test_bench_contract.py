@@ -30,6 +30,28 @@ def test_reference_arm_prints_the_contract_line():
     assert "workload" in d["config"]
 
 
+def test_reference_arm_uses_all_cores_and_never_loads_the_product():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers: the arm must still use every host core (the
+    N>1 reference ratios were inflated ~20x by a 1-thread arm), and it must not load librtb200.so (RTB200_LIB points
+    at a file that does not exist: any call into the product would raise)."""
+    r = _run("--impl", "reference", "--n-spheres", "20000", "--steps", "1", "--warmup", "0",
+             env={"OMP_NUM_THREADS": "1", "RTB200_LIB": "/nonexistent/librtb200.so"})
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    assert d["cpu_baseline"]["cores"] == os.cpu_count() or d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert list(d["config"].keys()) == ["workload"]  # nothing the product arm's config does not have
+
+
+def test_terrain_ramp_restatement_matches_the_reference_table():
+    """bench.py's numpy ramp (reference arm: no product, no oracle/_ref) against ColorRamp.cuh's own bake (golden)."""
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    import bench
+    gold = np.load(os.path.join(HERE, "golden", "ref_color_ramp.npz"))
+    for n in (1, 2, 7, 500):
+        assert np.allclose(bench.terrain_ramp_numpy(n), gold[f"terrain_{n}"], rtol=0, atol=2e-7), n
+
+
 def test_reference_arm_other_ranks_exit_quietly():
     r = _run("--impl", "reference", "--gpus", "2", "--n-spheres", "20000", "--steps", "1", "--warmup", "0",
              env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
