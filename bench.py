@@ -533,12 +533,12 @@ def run_ours(a):
         if world_size == 1 and not a.no_build_100m:
             sc.close()
             sc = None
-            del accum, rgba8
             torch.cuda.empty_cache()
             try:
                 line["build_100m"] = build_100m(pkg, synth, torch, dev, ctx, stream, peak)
             except Exception as e:  # noqa: BLE001 - the headline number must still be printed
                 line["build_100m"] = {"error": repr(e)}
+        print(json.dumps(line), flush=True)
     if xch is not None:
         xch.close()
     if world_size > 1:

@@ -41,8 +41,7 @@ typedef struct {
     int mesh, cache, debug_mode;
     uint64_t thread_count;                 /* cache-process-thread-count */
     const char *series_path, *series_name, *cache_path, *stl_path, *preset;
-    /* materials and extra geometry (ProgramArgumentParser.cu:4-39,63-80); "triangles" is ignored
-     * exactly as the reference ignores it */
+    /* materials and extra geometry (ProgramArgumentParser.cu:4-39,63-80) */
     uint32_t n_rough, n_metal, n_sphere;
     const float *roughs;                   /* [n_rough][3] */
     const float *metals;                   /* [n_metal][4] albedo + fuzz */
@@ -62,6 +61,13 @@ typedef struct {
     uint32_t spp, max_depth;
     uint64_t seed, frames;
     const char *output;
+    /* "triangles" (docs/configuration.md:232-247; documented, never parsed by the reference: SURVEY §C quirk 10):
+     * world-space triangles that follow the config spheres in instance (SBT) order */
+    uint32_t n_triangle;
+    const float *triangle_vertices;        /* [n_triangle][9] */
+    const float *triangle_normals;         /* [n_triangle][9] per-vertex normals */
+    const int32_t *triangle_mat_type;
+    const uint64_t *triangle_mat_index;
 } rt_io_config_view;
 int rt_io_config_load(const char *path, rt_io_config *out);
 int rt_io_config_parse(const char *json_text, rt_io_config *out);

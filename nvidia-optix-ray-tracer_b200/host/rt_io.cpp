@@ -32,6 +32,9 @@ struct rt_io_config_s {
     std::vector<float> roughs, metals, sphere_cr, sphere_tf;
     std::vector<int32_t> sphere_mt;
     std::vector<uint64_t> sphere_mi;
+    std::vector<float> tri_v, tri_n;
+    std::vector<int32_t> tri_mt;
+    std::vector<uint64_t> tri_mi;
     rt_io_config_view v{};
 };
 
@@ -72,7 +75,25 @@ void parse_config(const std::string &text, rt_io_config_s &c) {
         rt_construct_transform(sh, ro, sc, tf);
         c.sphere_tf.insert(c.sphere_tf.end(), tf, tf + 12);
     }
-    // "triangles" is documented (docs/configuration.md:232-247) but never parsed by the reference.
+    // "triangles" is documented (docs/configuration.md:232-247) but never parsed by the reference, whose upload path
+    // for them is dead code with an index bug (RendererMesh.cu:49,52: currentTriangles[i] instead of [j]; SURVEY §C
+    // quirk 10).  Implemented behind the documented schema: vertices / normals as 3 x [x,y,z], mat-type, mat-index.
+    if (d.contains("triangles")) {
+        for (const auto &t : *d.at("triangles").arr) {
+            for (const char *key : {"vertices", "normals"}) {
+                const auto &rows = *t.at(key).arr;
+                if (rows.size() != 3) raise(RT_IO_ERR_PARSE, std::string("config: triangle '") + key + "' needs 3 rows");
+                for (const auto &row : rows) {
+                    const auto a = row.as_floats();
+                    if (a.size() < 3) raise(RT_IO_ERR_PARSE, std::string("config: triangle '") + key + "' rows need 3 numbers");
+                    std::vector<float> &dst = key[0] == 'v' ? c.tri_v : c.tri_n;
+                    dst.insert(dst.end(), {a[0], a[1], a[2]});
+                }
+            }
+            c.tri_mt.push_back(t.at("mat-type").as_string() == "ROUGH" ? RT_MAT_ROUGH : RT_MAT_METAL);
+            c.tri_mi.push_back((uint64_t)t.at("mat-index").as_number());
+        }
+    }
     const rtjson::Value &l = d.at("loop-data");
     c.api = l.at("api").as_string();
     if (c.api != "OGL" && c.api != "VK" && c.api != "D3D11" && c.api != "D3D12")
@@ -123,6 +144,11 @@ void parse_config(const std::string &text, rt_io_config_s &c) {
     v.sphere_mat_type = c.sphere_mt.data();
     v.sphere_mat_index = c.sphere_mi.data();
     v.sphere_transform = c.sphere_tf.data();
+    v.n_triangle = (uint32_t)c.tri_mt.size();
+    v.triangle_vertices = c.tri_v.data();
+    v.triangle_normals = c.tri_n.data();
+    v.triangle_mat_type = c.tri_mt.data();
+    v.triangle_mat_index = c.tri_mi.data();
 }
 
 }  // namespace

@@ -7,6 +7,12 @@
 //   rtb200_render CONFIG.json [--out DIR] [--width W] [--height H] [--spp N] [--depth D] [--seed S]
 //                 [--max-files K] [--frame-stride S] [--max-frames F] [--extra-series NAME]...
 //                 [--spheres] [--drop-shape ID]... [--format pfm|exr|ppm|none] [--device N] [--quiet]
+//                 [--aov]     also write the first-hit albedo and normal buffers (the reference's denoiser guides,
+//                             shader/Shader.cu:270-272, src/Global/RendererImpl.cu:680-711) as <stem>_albedo / <stem>_normal
+//                             images and the primary-hit primitive ids as <stem>_primid.u32 (raw little-endian u32, row-major)
+//                 [--compat]  reference shading quirks 1+2 (scene option compat_shading = 3) and the reference's transport
+//                             details (RT_FLAG_REF_NO_SELF_SKIP | RT_FLAG_REF_MUL_ON_RETURN): the reference's own pixels
+//                 [--fused]   the queue-free persistent path kernel (scene option fused = 1)
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -33,7 +39,7 @@ struct Options {
     int width = 0, height = 0, device = 0;
     long spp = -1, depth = -1, max_files = -1, frame_stride = 1, max_frames = -1;
     long long seed = -1;
-    bool spheres = false, quiet = false;
+    bool spheres = false, quiet = false, aov = false, compat = false, fused = false;
     std::vector<std::string> extra_series;
     std::set<uint64_t> drop_shapes;
 };
@@ -86,6 +92,9 @@ Options parse_args(int argc, char **argv) {
         else if (a == "--device") o.device = atoi(val());
         else if (a == "--spheres") o.spheres = true;
         else if (a == "--quiet") o.quiet = true;
+        else if (a == "--aov") o.aov = true;
+        else if (a == "--compat") o.compat = true;
+        else if (a == "--fused") o.fused = true;
         else if (!a.empty() && a[0] != '-' && o.config.empty()) o.config = a;
         else die(1, "unknown argument %s", a.c_str());
     }
@@ -143,15 +152,51 @@ TimeSeries load_time_series(const std::string &dir, const std::string &name, siz
 
 struct Frame {
     float *d_accum = nullptr, *d_color = nullptr;
+    float *d_albedo = nullptr, *d_normal = nullptr;  // --aov
+    uint32_t *d_primid = nullptr;
     uint8_t *d_rgba8 = nullptr;
     std::vector<float> h_color;
     std::vector<uint8_t> h_rgba8;
     uint32_t w = 0, h = 0;
 };
 
+// first-hit albedo / normal (float4 per pixel; the normal is written as n * 0.5 + 0.5 into PPM, raw into PFM / EXR)
+// and primary-hit primitive ids
+void write_aovs(const Options &o, Frame &fr, int flip_y, const std::string &stem, cudaStream_t st) {
+    const size_t n = (size_t)fr.w * fr.h;
+    for (int which = 0; which < 2; which++) {
+        const std::string name = o.out + stem + (which ? "_normal" : "_albedo");
+        CU(cudaMemcpyAsync(fr.h_color.data(), which ? fr.d_normal : fr.d_albedo, 16 * n, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (o.format == "ppm") {
+            for (size_t i = 0; i < n; i++) {
+                for (int c = 0; c < 3; c++) {
+                    float v = fr.h_color[4 * i + c];
+                    if (which) v = v * 0.5f + 0.5f;
+                    fr.h_rgba8[4 * i + c] = (uint8_t)std::min(255.0f, std::max(0.0f, v * 256.0f));
+                }
+                fr.h_rgba8[4 * i + 3] = 255;
+            }
+            IO(rt_io_write_ppm((name + ".ppm").c_str(), fr.w, fr.h, fr.h_rgba8.data(), flip_y));
+        } else if (o.format == "exr") {
+            IO(rt_io_write_exr((name + ".exr").c_str(), fr.w, fr.h, fr.h_color.data(), flip_y));
+        } else {
+            IO(rt_io_write_pfm((name + ".pfm").c_str(), fr.w, fr.h, fr.h_color.data(), flip_y));
+        }
+    }
+    std::vector<uint32_t> ids(n);
+    CU(cudaMemcpyAsync(ids.data(), fr.d_primid, 4 * n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const std::string name = o.out + stem + "_primid.u32";
+    FILE *f = fopen(name.c_str(), "wb");
+    if (!f || fwrite(ids.data(), 4, n, f) != n) die(2, "cannot write %s", name.c_str());
+    fclose(f);
+}
+
 void write_frame(const Options &o, Frame &fr, rt_context ctx, int flip_y, const std::string &stem, cudaStream_t st) {
     if (o.format == "none") return;
     const size_t n = (size_t)fr.w * fr.h;
+    if (o.aov) write_aovs(o, fr, flip_y, stem, st);
     if (o.format == "ppm") {
         RT(rt_resolve(ctx, fr.d_accum, n, nullptr, fr.d_rgba8, st));
         CU(cudaMemcpyAsync(fr.h_rgba8.data(), fr.d_rgba8, 4 * n, cudaMemcpyDeviceToHost, st));
@@ -196,6 +241,7 @@ void set_materials(rt_scene scene, const rt_io_config_view &cfg, size_t max_part
 
 struct ConfigSpheres {
     std::vector<float *> d_center, d_radius;
+    float *d_tri_v = nullptr, *d_tri_n = nullptr;  // config "triangles"
 };
 // GeometryData.spheres: one single-sphere group + one instance each (RendererTime.cu:74-85,116-119).
 // Every sphere gets its own JSON transform (the reference's user hook only refreshes instance 0,
@@ -210,6 +256,17 @@ void add_config_spheres(rt_scene scene, const rt_io_config_view &cfg, ConfigSphe
         uint32_t g = 0;
         RT(rt_scene_add_spheres(scene, cs.d_center[i], cs.d_radius[i], 1, &g));
         RT(rt_scene_add_instance(scene, g, cfg.sphere_transform + 12 * i, cfg.sphere_mat_type[i], (uint32_t)cfg.sphere_mat_index[i], 0, nullptr));
+    }
+    // GeometryData.triangles follow the spheres in SBT order (RendererMesh.cu:110-118): one world-space triangle
+    // group + identity instance each (the reference's upload of them is dead code)
+    if (cfg.n_triangle && !cs.d_tri_v) {
+        cs.d_tri_v = to_device(cfg.triangle_vertices, 9 * (size_t)cfg.n_triangle);
+        cs.d_tri_n = to_device(cfg.triangle_normals, 9 * (size_t)cfg.n_triangle);
+    }
+    for (uint32_t i = 0; i < cfg.n_triangle; i++) {
+        uint32_t g = 0;
+        RT(rt_scene_add_triangles(scene, cs.d_tri_v + 9 * (size_t)i, cs.d_tri_n + 9 * (size_t)i, 1, &g));
+        RT(rt_scene_add_instance(scene, g, nullptr, cfg.triangle_mat_type[i], (uint32_t)cfg.triangle_mat_index[i], 0, nullptr));
     }
 }
 
@@ -227,7 +284,8 @@ void render_and_write(const Options &o, const rt_io_config_view &cfg, rt_scene s
     fp.background[0] = 0.7f;                            // RendererTime.cu:245-247 / RendererMesh.cu:260-262
     fp.background[1] = 0.8f;
     fp.background[2] = 0.9f;
-    rt_outputs out{fr.d_accum, nullptr, nullptr, nullptr};
+    if (o.compat) fp.flags |= RT_FLAG_REF_NO_SELF_SKIP | (depth <= 5 ? RT_FLAG_REF_MUL_ON_RETURN : 0u);
+    rt_outputs out{fr.d_accum, o.aov ? fr.d_albedo : nullptr, o.aov ? fr.d_normal : nullptr, o.aov ? fr.d_primid : nullptr};
     RT(rt_render(scene, &cam, &fp, &out, st));
     write_frame(o, fr, g_ctx, cfg.flip_up ? 0 : 1, stem, st);
     rt_stats stt;
@@ -305,7 +363,7 @@ int run_time_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
             for (size_t k = 0; k < cur->n; k++)
                 if (!o.drop_shapes.count(cur->shape_id[k])) parts.push_back({cur, next, k});
         }
-        uint32_t first_particle = cfg.n_sphere, sphere_group = 0;
+        uint32_t first_particle = cfg.n_sphere + cfg.n_triangle, sphere_group = 0;
         if (o.spheres) {
             // BASELINE config 1 mapping: particle -> analytic sphere, centre = POINTS, r = size / 2 (0.05 when absent)
             sph_c.assign(3 * parts.size(), 0.0f);
@@ -417,7 +475,7 @@ int run_mesh_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
         for (size_t f = 0; f < frames; f += (size_t)o.frame_stride) {
             for (size_t k = 0; k < mv.n_particles; k++)
                 rt_transform_mesh(mv.vel + 3 * k, dur, frames, f, cfg.particle_shift, cfg.particle_scale, &tf[12 * k]);
-            if (mv.n_particles) RT(rt_scene_set_transforms(scene, tf.data(), cfg.n_sphere, mv.n_particles, st));
+            if (mv.n_particles) RT(rt_scene_set_transforms(scene, tf.data(), cfg.n_sphere + cfg.n_triangle, mv.n_particles, st));
             char stem[64];
             snprintf(stem, sizeof stem, "frame_%05zu_%03zu", fi, f);
             render_and_write(o, cfg, scene, fr, cam, st, spp, depth, seed, frame_total, stem, rs);
@@ -456,6 +514,13 @@ int main(int argc, char **argv) {
     const size_t n = (size_t)fr.w * fr.h;
     CU(cudaMalloc(&fr.d_accum, 16 * n));
     CU(cudaMalloc(&fr.d_rgba8, 4 * n));
+    if (o.aov) {
+        CU(cudaMalloc(&fr.d_albedo, 16 * n));
+        CU(cudaMalloc(&fr.d_normal, 16 * n));
+        CU(cudaMalloc(&fr.d_primid, 4 * n));
+    }
+    if (o.compat) RT(rt_scene_set_option(scene, "compat_shading", 3));
+    if (o.fused) RT(rt_scene_set_option(scene, "fused", 1));
     fr.h_color.resize(4 * n);
     fr.h_rgba8.resize(4 * n);
     rt_camera cam;

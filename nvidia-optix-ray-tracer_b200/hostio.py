@@ -41,7 +41,9 @@ class ConfigView(C.Structure):
                 ("particle_shift", _f3), ("particle_scale", _f3),
                 ("mouse_sensitivity", C.c_float), ("camera_pitch_limit_degree", C.c_float), ("camera_speed_stride", C.c_float),
                 ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("seed", C.c_uint64), ("frames", C.c_uint64),
-                ("output", C.c_char_p)]
+                ("output", C.c_char_p),
+                ("n_triangle", C.c_uint32), ("triangle_vertices", _fp), ("triangle_normals", _fp),
+                ("triangle_mat_type", C.POINTER(C.c_int32)), ("triangle_mat_index", _u64p)]
 
 
 class ParticlesView(C.Structure):
@@ -159,6 +161,10 @@ def _config_dict(h):
     d["sphere_mat_type"] = _arr(v.sphere_mat_type, (v.n_sphere,), np.int32)
     d["sphere_mat_index"] = _arr(v.sphere_mat_index, (v.n_sphere,), np.uint64)
     d["sphere_transform"] = _arr(v.sphere_transform, (v.n_sphere, 12), np.float32)
+    d["triangle_vertices"] = _arr(v.triangle_vertices, (v.n_triangle, 3, 3), np.float32)
+    d["triangle_normals"] = _arr(v.triangle_normals, (v.n_triangle, 3, 3), np.float32)
+    d["triangle_mat_type"] = _arr(v.triangle_mat_type, (v.n_triangle,), np.int32)
+    d["triangle_mat_index"] = _arr(v.triangle_mat_index, (v.n_triangle,), np.uint64)
     return d
 
 

@@ -40,6 +40,13 @@ def config_for(d, mesh, series):
     return c
 
 
+def add_config_triangles(sd, c):
+    """config "triangles": one world-space group + identity instance each, after the config spheres (SBT order)."""
+    for k in range(len(c["triangle_mat_type"])):
+        g = sd.add_triangles(c["triangle_vertices"][k], c["triangle_normals"][k])
+        sd.add_instance(g, None, int(c["triangle_mat_type"][k]), int(c["triangle_mat_index"][k]), 0)
+
+
 def run_driver(cfg_path, out, *extra):
     cmd = [DRIVER, cfg_path, "--out", out, "--width", str(W), "--height", str(H), "--spp", str(SPP), "--depth", str(DEPTH),
            "--seed", str(SEED), "--format", "pfm", "--quiet"] + list(extra)
@@ -89,6 +96,7 @@ def test_time_mode_driver_matches_oracle(tmp_path, pkg, hio, oracle):
             sd = scenes.SceneDesc(roughs, c["metals"])
             g0 = sd.add_spheres([[0, 0, 0]], [1000.0])
             sd.add_instance(g0, c["sphere_transform"][0], 1, 0, 0)
+            add_config_triangles(sd, c)
             gs = [sd.add_triangles(s["vertices"], s["vertex_normals"]) for s in shapes]
             for k in range(len(p["id"])):
                 qn = nxt["quat"][k] if k < len(nxt["id"]) else p["quat"][k]
@@ -108,13 +116,14 @@ def test_spheres_mapping_driver_matches_oracle(tmp_path, pkg, hio, oracle):
     parts = make_time_inputs(d)
     cfg = config_for(d, False, "t.vtk.series")
     json.dump(cfg, open(d + "config.json", "w"))
-    run_driver(d + "config.json", d + "out", "--spheres", "--max-frames", "1")
+    run_driver(d + "config.json", d + "out", "--spheres", "--max-frames", "1", "--aov")
     c = hio.load_config(d + "config.json")
     p = parts[0]
     roughs = np.concatenate([c["roughs"], pkg.bake_color_ramp("terrain", max(max(q["id"]) for q in parts) + 1)])
     sd = scenes.SceneDesc(roughs, c["metals"])
     g0 = sd.add_spheres([[0, 0, 0]], [1000.0])
     sd.add_instance(g0, c["sphere_transform"][0], 1, 0, 0)
+    add_config_triangles(sd, c)
     for k in range(len(p["id"])):
         t = pkg.transform_time(p["pos"][k], p["vel"][k], p["quat"][k], p["quat"][k], np.float32(0.01), 9, 0, c["particle_shift"], c["particle_scale"])
         g = sd.add_spheres([[0, 0, 0]], [0.1])
@@ -124,6 +133,13 @@ def test_spheres_mapping_driver_matches_oracle(tmp_path, pkg, hio, oracle):
     got = hio.read_pfm(d + "out/frame_00000_000.pfm")
     want = (o["accum"][:, :3] * np.float32(1.0 / SPP)).reshape(H, W, 3)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    # --aov: the denoiser guide buffers of the reference (Shader.cu:270-272) and the primary-hit ids, as files
+    alb, nrm = hio.read_pfm(d + "out/frame_00000_000_albedo.pfm"), hio.read_pfm(d + "out/frame_00000_000_normal.pfm")
+    assert np.array_equal(alb.view(np.uint32), o["albedo"][:, :3].reshape(H, W, 3).view(np.uint32))
+    assert np.array_equal(nrm.view(np.uint32), o["normal"][:, :3].reshape(H, W, 3).view(np.uint32))
+    ids = np.fromfile(d + "out/frame_00000_000_primid.u32", dtype="<u4")
+    assert np.array_equal(ids, o["prim_id"]) and len(set(ids.tolist())) > 4
+    assert (ids == 1).any() or (ids == 2).any()   # the config triangles (global ids 1 and 2) are visible
 
 
 def test_mesh_mode_driver_cache_then_render(tmp_path, pkg, hio, oracle):
@@ -155,6 +171,7 @@ def test_mesh_mode_driver_cache_then_render(tmp_path, pkg, hio, oracle):
             sd = scenes.SceneDesc(roughs, c["metals"])
             g0 = sd.add_spheres([[0, 0, 0]], [1000.0])
             sd.add_instance(g0, c["sphere_transform"][0], 1, 0, 0)
+            add_config_triangles(sd, c)
             for k in range(3):
                 a, b = int(m["vertex_offset"][k]), int(m["vertex_offset"][k + 1])
                 g = sd.add_triangles(m["vertices"][a:b], m["normals"][a:b])

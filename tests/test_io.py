@@ -23,7 +23,10 @@ CONFIG = {
                  "shift": [0.0, 0.0, -1000.5], "rotate": [0.0, 0.0, 0.0], "scale": [1.0, 1.0, 1.0]},
                 {"center": [1.0, 2.0, 3.0], "radius": 0.5, "mat-type": "METAL", "mat-index": 0,
                  "shift": [0.1, 0.2, 0.3], "rotate": [10.0, 20.0, 30.0], "scale": [2.0, 2.0, 2.0]}],
-    "triangles": [{"ignored": True}],
+    "triangles": [{"vertices": [[-0.6, -0.6, -0.45], [0.6, -0.6, -0.45], [0.6, 0.6, -0.45]],
+                   "normals": [[0, 0, 1], [0, 0, 1], [0, 0, 1]], "mat-type": "METAL", "mat-index": 0},
+                  {"vertices": [[-0.6, -0.6, -0.45], [0.6, 0.6, -0.45], [-0.6, 0.6, -0.45]],
+                   "normals": [[0, 0, 1], [0.1, 0, 0.9], [0, 0.1, 0.9]], "mat-type": "ROUGH", "mat-index": 1}],
     "loop-data": {"api": "VK", "window-width": 1200, "window-height": 800, "fps": 240, "camera-center": [5.0, 0.0, 0.0],
                   "camera-target": [0.0, 0.0, 0.0], "up-direction": [0.0, 0.0, 1.0], "camera-pitch-limit-degree": 85.0,
                   "camera-speed-stride": 0.002, "camera-initial-speed-ratio": 10, "mouse-sensitivity": 0.002,
@@ -61,6 +64,17 @@ def test_config_schema(hio, pkg, built_lib):
     for i, s in enumerate(CONFIG["spheres"]):
         want = np.float32(pkg.construct_transform(s["shift"], s["rotate"], s["scale"]))
         assert np.array_equal(c["sphere_transform"][i].view(np.uint32), want.view(np.uint32))
+    # "triangles": documented (docs/configuration.md:232-247), dead in the reference, parsed here
+    assert c["triangle_vertices"].shape == (2, 3, 3) and np.array_equal(c["triangle_mat_type"], [pkg.RT_MAT_METAL, pkg.RT_MAT_ROUGH])
+    assert np.array_equal(c["triangle_mat_index"], [0, 1])
+    assert np.allclose(c["triangle_vertices"][1], CONFIG["triangles"][1]["vertices"]) and np.allclose(c["triangle_normals"][1], CONFIG["triangles"][1]["normals"])
+    no_tri = {k: v for k, v in CONFIG.items() if k != "triangles"}
+    assert len(hio.parse_config(json.dumps(no_tri))["triangle_mat_type"]) == 0 and len(hio.parse_config(json.dumps(dict(CONFIG, triangles=[])))["triangle_mat_type"]) == 0
+    for bad_tri in ({"vertices": [[0, 0, 0]], "normals": [[0, 0, 1]] * 3, "mat-type": "ROUGH", "mat-index": 0},
+                    {"vertices": [[0, 0, 0]] * 3, "normals": [[0, 0]] * 3, "mat-type": "ROUGH", "mat-index": 0},
+                    {"vertices": [[0, 0, 0]] * 3, "normals": [[0, 0, 1]] * 3, "mat-index": 0}):
+        with pytest.raises(hio.IoError):
+            hio.parse_config(json.dumps(dict(CONFIG, triangles=[bad_tri])))
     assert np.allclose(c["particle_shift"], [0, 0.1, 0]) and np.allclose(c["camera_center"], [5, 0, 0])
     assert (c["spp"], c["max_depth"], c["seed"], c["frames"], c["output"]) == (1, 5, 0, 0, "")   # additive keys default
     c2 = hio.parse_config(json.dumps(dict(CONFIG, spp=16, seed=7, output="out/", frames=3, **{"max-depth": 8})))
