@@ -173,6 +173,13 @@ int rt_scene_add_instance(rt_scene scene, uint32_t group, const float *transform
  * (RendererTime.cu:436-480).  transforms = float[12*n], host (pinned or pageable) or device. */
 int rt_scene_set_transforms(rt_scene scene, const float *transforms, size_t first_instance,
                             size_t n, void *stream);
+/* The same without a host round trip, for particle counts where RendererTime.cu:436-480's per-frame host loop
+ * + H2D copy is the bottleneck: dev_transforms = float[12*n] in device memory (e.g. written by
+ * rt_transforms_time).  The array is READ BY EVERY FOLLOWING rt_accel_build, on that build's stream, over the
+ * uploaded instance table — it must stay allocated, and hold this frame's values in stream order, until a later
+ * call for the same instances (either form) or rt_scene_clear_geometry replaces it.  Sphere groups need
+ * similarity transforms (uniform scale); that is checked for host-side transforms only. */
+int rt_scene_set_transforms_device(rt_scene scene, const float *dev_transforms, size_t first_instance, size_t n);
 
 /* ---- accel: replaces buildASImpl + buildIAS + updateIAS (RendererImpl.cu:30-88,174-242) -----
  * Flattens instances to world space and rebuilds the LBVH (30-bit Morton, radix sort, Karras
@@ -192,6 +199,19 @@ int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float
                       const float *dev_velocities, size_t n, float duration, size_t frames_this_file,
                       size_t frame, const float particle_shift[3], const float particle_scale[3],
                       float *dev_centers_out, float *dev_radii_out, void *stream);
+
+/* Time-mode per-frame instance transforms on the device: replaces the host loop of RendererTime.cu:283-293
+ *      (position + velocity * t, slerp :297-340 of the file's two key-frame quaternions, quatToEuler :343-370,
+ *      constructTransformMatrix DeviceFunctions.cuh:133-148) for n particles at once.  Inputs are device arrays:
+ *      positions / velocities float[3n], quaternions float[4n] {x,y,z,w} (16-byte aligned); output float[12n]
+ *      row-major 3x4 (16-byte aligned), ready for rt_scene_set_transforms_device.  Same operation order as
+ *      rt_transform_time: the translation column is bit-identical to it; the rotation entries go through the CUDA
+ *      libm's sinf/cosf/acosf/asinf/atan2f instead of glibc's and differ by <= 4e-6 absolute (tests/test_gpu_build.py).
+ *      Parity configs (C1-C3) therefore keep rt_transform_time on the host; this is the at-scale path. */
+int rt_transforms_time(rt_context ctx, const float *dev_positions, const float *dev_velocities,
+                       const float *dev_quat_cur, const float *dev_quat_next, size_t n, float duration,
+                       size_t frames_this_file, size_t frame, const float particle_shift[3],
+                       const float particle_scale[3], float *dev_transforms_out, void *stream);
 
 /* ---- launch: replaces optixLaunch(pipeline, stream, params, sbt, w, h, 1) and the raygen /
  *      closest-hit / miss programs of shader/Shader.cu ---------------------------------------- */

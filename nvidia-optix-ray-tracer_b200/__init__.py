@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "rt_scene_set_transforms", "rt_accel_build", "rt_render", "rt_resolve", "rt_get_stats",
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
-    "rt_spheres_advect", "rt_render_primary", "rt_scene_set_primary_hits", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
+    "rt_spheres_advect", "rt_transforms_time", "rt_scene_set_transforms_device", "rt_render_primary", "rt_scene_set_primary_hits", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
 ]
 RT_MAX_PARTS = 16
 RT_PEER_HANDLE_BYTES = 64
@@ -108,6 +108,8 @@ def lib() -> C.CDLL:
         L.rt_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(FrameParams), C.POINTER(Outputs), vp]
         L.rt_resolve.argtypes = [vp, vp, sz, vp, vp, vp]
         L.rt_spheres_advect.argtypes = [vp, vp, vp, vp, sz, C.c_float, sz, sz, f_p, f_p, vp, vp, vp]
+        L.rt_transforms_time.argtypes = [vp, vp, vp, vp, vp, sz, C.c_float, sz, sz, f_p, f_p, vp, vp]
+        L.rt_scene_set_transforms_device.argtypes = [vp, vp, sz, sz]
         L.rt_render_primary.argtypes = [vp, C.POINTER(Camera), u32, u32, sz, sz, vp, vp]
         L.rt_scene_set_primary_hits.argtypes = [vp, vp]
         L.rt_peer_alloc.argtypes = [vp, sz, C.POINTER(vp), C.c_char_p]
@@ -192,6 +194,12 @@ class Context:
                                            _fa(pscale), out_c_ptr, out_r_ptr, stream))
 
     # ---- multi-GPU exchange step (include/rtb200.h "rt_peer_*", "rt_resolve_parts")
+    def transforms_time(self, pos_ptr, vel_ptr, quat_cur_ptr, quat_next_ptr, n, duration, frames, frame, pshift, pscale, out_ptr,
+                        stream=None):
+        """Device form of transform_time for n particles (include/rtb200.h rt_transforms_time)."""
+        self.check(lib().rt_transforms_time(self._h, pos_ptr, vel_ptr, quat_cur_ptr, quat_next_ptr, n, duration, frames, frame,
+                                            _fa(pshift), _fa(pscale), out_ptr, stream))
+
     def peer_alloc(self, nbytes: int):
         """(device pointer, 64-byte handle) of a buffer other processes can map with peer_open."""
         ptr = C.c_void_p()
@@ -261,6 +269,9 @@ class Scene:
 
     def set_transforms(self, transforms_ptr, first, n, stream=None):
         self.ctx.check(lib().rt_scene_set_transforms(self._h, transforms_ptr, first, n, stream))
+
+    def set_transforms_device(self, transforms_ptr, first, n):
+        self.ctx.check(lib().rt_scene_set_transforms_device(self._h, transforms_ptr, first, n))
 
     def build(self, stream=None):
         self.ctx.check(lib().rt_accel_build(self._h, stream))

@@ -199,6 +199,7 @@ int rt_scene_clear_geometry(rt_scene scene) {
     Scene &s = scene->s;
     s.groups.clear();
     s.insts.clear();
+    s.dev_tf.clear();
     s.built = false;
     return RT_OK;
 }
@@ -259,6 +260,20 @@ int rt_scene_set_transforms(rt_scene scene, const float *transforms, size_t firs
         memcpy(in.m, src + 12 * i, sizeof in.m);
         in.identity = linear_is_identity(in.m) ? 1u : 0u;
     }
+    // values set here replace any device-resident range that covers the same instances
+    for (size_t k = s.dev_tf.size(); k-- > 0;)
+        if (s.dev_tf[k].first < first + n && first < s.dev_tf[k].first + s.dev_tf[k].n) s.dev_tf.erase(s.dev_tf.begin() + k);
+    s.built = false;
+    return RT_OK;
+}
+
+int rt_scene_set_transforms_device(rt_scene scene, const float *dev_transforms, size_t first, size_t n) {
+    if (!scene || (n && !dev_transforms)) return RT_ERR_INVALID;
+    Scene &s = scene->s;
+    if (first + n > s.insts.size()) return set_error(s.ctx, RT_ERR_INVALID, "instances [%zu,%zu) out of range", first, first + n);
+    for (size_t k = s.dev_tf.size(); k-- > 0;)
+        if (s.dev_tf[k].first < first + n && first < s.dev_tf[k].first + s.dev_tf[k].n) s.dev_tf.erase(s.dev_tf.begin() + k);
+    if (n) s.dev_tf.push_back(rtb::DevTransforms{dev_transforms, first, n});
     s.built = false;
     return RT_OK;
 }
@@ -304,6 +319,16 @@ int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float
     DeviceGuard g(ctx->c.device);
     return rtb::spheres_advect(&ctx->c, dev_base_centers, dev_base_radii, dev_velocities, n, duration, frames_this_file, frame,
                                particle_shift, particle_scale, dev_centers_out, dev_radii_out, (cudaStream_t)stream);
+}
+
+int rt_transforms_time(rt_context ctx, const float *dev_positions, const float *dev_velocities, const float *dev_quat_cur,
+                       const float *dev_quat_next, size_t n, float duration, size_t frames_this_file, size_t frame,
+                       const float particle_shift[3], const float particle_scale[3], float *dev_transforms_out, void *stream) {
+    if (!ctx || !particle_shift || !particle_scale || !frames_this_file) return RT_ERR_INVALID;
+    if (n && (!dev_positions || !dev_velocities || !dev_quat_cur || !dev_quat_next || !dev_transforms_out)) return RT_ERR_INVALID;
+    DeviceGuard g(ctx->c.device);
+    return rtb::transforms_time(&ctx->c, dev_positions, dev_velocities, dev_quat_cur, dev_quat_next, n, duration, frames_this_file,
+                                frame, particle_shift, particle_scale, dev_transforms_out, (cudaStream_t)stream);
 }
 
 int rt_peer_alloc(rt_context ctx, size_t bytes, void **dev_ptr_out, unsigned char handle_out[RT_PEER_HANDLE_BYTES]) {

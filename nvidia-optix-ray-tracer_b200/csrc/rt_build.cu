@@ -1022,6 +1022,147 @@ int spheres_advect(Context *ctx, const float *base_c, const float *base_r, const
     return RT_OK;
 }
 
+// ------------------------------------------------------------------ per-frame particle transforms (Time mode)
+// src/Global/RendererTime.cu:283-293 (position + velocity * time, slerp of the two key-frame quaternions, :297-340,
+// quatToEuler :343-370) followed by constructTransformMatrix (DeviceFunctions.cuh:133-148: T * (Rx*Ry*Rz) * S with the
+// 4x4 products accumulated from 0 in ascending n).  Same operation order as the host chain in rt_host.cpp; the
+// translation column is bit-identical to it, the rotation entries differ by the CUDA libm's sinf / cosf / acosf /
+// asinf / atan2f against glibc's (<= 2 ulp each: <= 4e-6 absolute on a matrix entry, tests/test_gpu_build.py).
+struct M4 {
+    float v[4][4];
+};
+__device__ __forceinline__ M4 m4_identity() {
+    M4 m;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) m.v[i][j] = (i == j) ? 1.0f : 0.0f;
+    return m;
+}
+__device__ __forceinline__ M4 m4_mul(const M4 &a, const M4 &b) {
+    M4 r;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int n = 0; n < 4; n++) acc += a.v[i][n] * b.v[n][j];
+            r.v[i][j] = acc;
+        }
+    return r;
+}
+template <int kAxis>
+__device__ __forceinline__ M4 m4_rotation(float degree) {
+    constexpr float kPiRef = 3.1415926;  // DeviceFunctions.cuh:20
+    const float theta = degree * kPiRef / 180.0f;
+    const float c = cosf(theta), s = sinf(theta);
+    M4 m = m4_identity();
+    constexpr int a = (kAxis + 1) % 3, b = (kAxis + 2) % 3;
+    m.v[a][a] = c;
+    m.v[a][b] = -s;
+    m.v[b][a] = s;
+    m.v[b][b] = c;
+    return m;
+}
+__global__ void __launch_bounds__(128)
+k_transforms_time(const float *__restrict__ pos, const float *__restrict__ vel, const float4 *__restrict__ quat_cur,
+                  const float4 *__restrict__ quat_next, size_t n, float duration, float frames, float frame, float factor,
+                  F3 pshift, F3 pscale, float4 *__restrict__ out) {
+    constexpr float kPiRef = 3.1415926;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float sh[3] = {pshift.x, pshift.y, pshift.z};
+    float shift[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float total = vel[3 * i + a] * duration;
+        const float per_frame = total / frames;
+        const float here = pos[3 * i + a] + per_frame * frame;
+        shift[a] = sh[a] + here;
+    }
+    // slerp with the reference's positional return: q = {x, y, z, w} in, {w-, x-, y-, z-expression} out
+    const float4 qa = quat_cur[i];
+    float4 qb = quat_next[i];
+    float dp = qa.w * qb.w + qa.x * qb.x + qa.y * qb.y + qa.z * qb.z;
+    if (dp < 0.0f) {
+        qb = make_float4(-qb.x, -qb.y, -qb.z, -qb.w);
+        dp = -dp;
+    }
+    float q0, q1, q2, q3;
+    if (dp > 0.9995f) {
+        float rx = qa.w + factor * (qb.w - qa.w);
+        float ry = qa.x + factor * (qb.x - qa.x);
+        float rz = qa.y + factor * (qb.y - qa.y);
+        float rw = qa.z + factor * (qb.z - qa.z);
+        const float mag = sqrtf(rw * rw + rx * rx + ry * ry + rz * rz);
+        if (mag > 0.0f) {
+            rw /= mag; rx /= mag; ry /= mag; rz /= mag;
+        }
+        q0 = rx; q1 = ry; q2 = rz; q3 = rw;
+    } else {
+        const float theta0 = acosf(dp);
+        const float theta = theta0 * factor;
+        const float st = sinf(theta), st0 = sinf(theta0);
+        const float k0 = cosf(theta) - dp * st / st0;
+        const float k1 = st / st0;
+        q0 = (k0 * qa.w) + (k1 * qb.w);
+        q1 = (k0 * qa.x) + (k1 * qb.x);
+        q2 = (k0 * qa.y) + (k1 * qb.y);
+        q3 = (k0 * qa.z) + (k1 * qb.z);
+    }
+    // quatToEuler on {x, y, z, w} = {q0, q1, q2, q3}, degrees
+    const float roll = atan2f(2 * (q3 * q0 + q1 * q2), 1 - 2 * (q0 * q0 + q1 * q1));
+    const float sp = 2 * (q3 * q1 - q2 * q0);
+    const float pitch = (fabsf(sp) >= 1) ? copysignf(kPiRef / 2, sp) : asinf(sp);
+    const float yaw = atan2f(2 * (q3 * q2 + q0 * q1), 1 - 2 * (q1 * q1 + q2 * q2));
+    const float ex = roll * 180.0f / kPiRef, ey = pitch * 180.0f / kPiRef, ez = yaw * 180.0f / kPiRef;
+
+    M4 T = m4_identity();
+    T.v[0][3] = shift[0]; T.v[1][3] = shift[1]; T.v[2][3] = shift[2];
+    const M4 R = m4_mul(m4_mul(m4_rotation<0>(ex), m4_rotation<1>(ey)), m4_rotation<2>(ez));
+    M4 S = m4_identity();
+    S.v[0][0] = pscale.x; S.v[1][1] = pscale.y; S.v[2][2] = pscale.z;
+    const M4 M = m4_mul(m4_mul(T, R), S);
+#pragma unroll
+    for (int r = 0; r < 3; r++) out[3 * i + r] = make_float4(M.v[r][0], M.v[r][1], M.v[r][2], M.v[r][3]);
+}
+
+int transforms_time(Context *ctx, const float *pos, const float *vel, const float *quat_cur, const float *quat_next, size_t n,
+                    float duration, size_t frames, size_t frame, const float *pshift, const float *pscale, float *out12,
+                    cudaStream_t st) {
+    if (!n) return RT_OK;
+    const size_t blocks = (n + 127) / 128;
+    if (blocks > 0x7FFFFFFFull) return set_error(ctx, RT_ERR_INVALID, "too many particles");
+    if ((((uintptr_t)quat_cur | (uintptr_t)quat_next | (uintptr_t)out12) & 15u) != 0)
+        return set_error(ctx, RT_ERR_INVALID, "rt_transforms_time: quaternion and output arrays must be 16-byte aligned");
+    float factor = 1.0f;  // RendererTime.cu:283-286
+    if (frames > 1) factor = (float)frame / (float)(frames - 1);
+    k_transforms_time<<<(unsigned)blocks, 128, 0, st>>>(pos, vel, reinterpret_cast<const float4 *>(quat_cur),
+                                                       reinterpret_cast<const float4 *>(quat_next), n, duration, (float)frames,
+                                                       (float)frame, factor, F3{pshift[0], pshift[1], pshift[2]},
+                                                       F3{pscale[0], pscale[1], pscale[2]}, reinterpret_cast<float4 *>(out12));
+    RT_CUDA(ctx, cudaGetLastError());
+    return RT_OK;
+}
+
+// Device-resident instance transforms (rt_scene_set_transforms_device): written over the uploaded instance table at
+// the start of every build, on the build's stream — no host round trip.
+__global__ void __launch_bounds__(256)
+k_apply_transforms(InstDev *__restrict__ insts, const float *__restrict__ tf, uint32_t first, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float m[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) m[k] = tf[12 * (size_t)i + k];
+    InstDev *in = insts + first + i;
+#pragma unroll
+    for (int k = 0; k < 12; k++) in->m[k] = m[k];
+    const bool ident = m[0] == 1.0f && m[1] == 0.0f && m[2] == 0.0f && m[4] == 0.0f && m[5] == 1.0f && m[6] == 0.0f &&
+                       m[8] == 0.0f && m[9] == 0.0f && m[10] == 1.0f;
+    in->identity = ident ? 1u : 0u;
+}
+
 // ------------------------------------------------------------------ host driver
 static inline uint32_t div_up(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 
@@ -1081,6 +1222,8 @@ int build_accel(Scene *s, cudaStream_t st) {
     if (!s->insts.empty())
         RT_CUDA(ctx, cudaMemcpyAsync(s->d_insts.p, s->insts.data(), s->insts.size() * sizeof(InstDev), cudaMemcpyHostToDevice, st));
     RT_CUDA(ctx, cudaMemcpyAsync(s->d_inst_base.p, base.data(), base.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    for (const DevTransforms &d : s->dev_tf)
+        if (d.n) k_apply_transforms<<<div_up((uint32_t)d.n, 256u), 256, 0, st>>>(s->d_insts.p, d.ptr, (uint32_t)d.first, (uint32_t)d.n);
     // pageable sources: the copies above are staged before returning, so `base` may die here.
 
     const size_t n1 = n ? n : 1;

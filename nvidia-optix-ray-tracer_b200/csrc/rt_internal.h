@@ -147,10 +147,15 @@ struct InstHost {
     InstDev d;
 };
 
+struct DevTransforms {  // rt_scene_set_transforms_device: float[12*n] on the device, applied at every build
+    const float *ptr;
+    size_t first, n;
+};
 struct Scene {
     Context *ctx = nullptr;
     std::vector<GroupDev> groups;
     std::vector<InstDev> insts;
+    std::vector<DevTransforms> dev_tf;
     bool topo_dirty = true;   // groups/instances changed -> re-upload tables
     bool built = false;
     uint32_t n_prims = 0, n_tris = 0;
@@ -254,5 +259,9 @@ SceneDev scene_dev(const Scene *s);
 int spheres_advect(Context *ctx, const float *base_c, const float *base_r, const float *vel, size_t n, float duration,
                    size_t frames, size_t frame, const float *pshift, const float *pscale, float *out_c, float *out_r,
                    cudaStream_t stream);
+
+int transforms_time(Context *ctx, const float *pos, const float *vel, const float *quat_cur, const float *quat_next, size_t n,
+                    float duration, size_t frames, size_t frame, const float *pshift, const float *pscale, float *out12,
+                    cudaStream_t stream);
 
 }  // namespace rtb

@@ -45,7 +45,7 @@ full)
   K=$1; shift
   CMD="$SHORT $*"
   timeout 600 $CMD > $O/${TAG}_plain.log 2>&1 && \
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:$K -s 1 -c 2 -o $O/${TAG}_full -f $CMD > $O/${TAG}_ncu.log 2>&1
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:$K -s ${SKIP:-1} -c ${COUNT:-2} -o $O/${TAG}_full -f $CMD > $O/${TAG}_ncu.log 2>&1
   echo "rc=$?"; tail -2 $O/${TAG}_ncu.log
   ;;
 localmem)
