@@ -5,7 +5,7 @@
 // no argv parsing at all (its config path is a compile-time constant, ProgramArgumentParser.cuh:41).
 //
 //   rtb200_render CONFIG.json [--out DIR] [--width W] [--height H] [--spp N] [--depth D] [--seed S]
-//                 [--max-files K] [--frame-stride S] [--max-frames F] [--extra-series NAME]...
+//                 [--max-files K] [--file-stride K] [--frame-stride S] [--max-frames F] [--extra-series NAME]...
 //                 [--spheres] [--drop-shape ID]... [--format pfm|exr|ppm|none] [--device N] [--quiet]
 //                 [--aov]     also write the first-hit albedo and normal buffers (the reference's denoiser guides,
 //                             shader/Shader.cu:270-272, src/Global/RendererImpl.cu:680-711) as <stem>_albedo / <stem>_normal
@@ -37,7 +37,7 @@ namespace {
 struct Options {
     std::string config, out = "out/", format = "pfm";
     int width = 0, height = 0, device = 0;
-    long spp = -1, depth = -1, max_files = -1, frame_stride = 1, max_frames = -1;
+    long spp = -1, depth = -1, max_files = -1, file_stride = 1, frame_stride = 1, max_frames = -1;
     long long seed = -1;
     bool spheres = false, quiet = false, aov = false, compat = false, fused = false;
     std::vector<std::string> extra_series;
@@ -63,6 +63,7 @@ struct Options {
     } while (0)
 
 rt_context g_ctx = nullptr;
+std::chrono::steady_clock::time_point g_t0;  // start of main(): RunStats.load_s = input loading (files, STL shapes, caches)
 #define RT(expr)                                                                  \
     do {                                                                          \
         if (int _rc = (expr)) die(4, "%s: error %d: %s", #expr, _rc, rt_last_error(g_ctx)); \
@@ -85,6 +86,7 @@ Options parse_args(int argc, char **argv) {
         else if (a == "--seed") o.seed = atoll(val());
         else if (a == "--max-files") o.max_files = atol(val());
         else if (a == "--frame-stride") o.frame_stride = std::max(1L, atol(val()));
+        else if (a == "--file-stride") o.file_stride = std::max(1L, atol(val()));  // render files 0, K, 2K, ... only
         else if (a == "--max-frames") o.max_frames = atol(val());
         else if (a == "--extra-series") o.extra_series.push_back(val());
         else if (a == "--drop-shape") o.drop_shapes.insert((uint64_t)atoll(val()));
@@ -225,8 +227,8 @@ namespace {
 
 struct RunStats {
     size_t frames = 0;
-    double build_ms = 0, render_ms = 0;
-    unsigned long long segments = 0;
+    double build_ms = 0, render_ms = 0, load_s = 0;
+    unsigned long long segments = 0, prims = 0;
 };
 
 // materials: config roughs ++ bakeColorRamp(preset, max particle count) (RendererTime.cu:235-243,
@@ -294,6 +296,7 @@ void render_and_write(const Options &o, const rt_io_config_view &cfg, rt_scene s
     rs.build_ms += stt.build_ms;
     rs.render_ms += stt.render_ms;
     rs.segments += stt.segments;
+    rs.prims += stt.n_prims;
     if (!o.quiet)
         fprintf(stderr, "%s: %llu prims, build %.3f ms, render %.3f ms, %.1f Mrays/s\n", stem.c_str(), (unsigned long long)stt.n_prims,
                 stt.build_ms, stt.render_ms, stt.render_ms > 0 ? stt.segments / stt.render_ms * 1e-3 : 0.0);
@@ -334,6 +337,7 @@ int run_time_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
             for (size_t k = 0; k < v.n; k++) max_particles = std::max<size_t>(max_particles, v.id[k] + 1);
         }
     set_materials(scene, cfg, max_particles);
+    rs.load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - g_t0).count();
 
     const uint32_t spp = o.spp > 0 ? (uint32_t)o.spp : cfg.spp, depth = o.depth > 0 ? (uint32_t)o.depth : cfg.max_depth;
     const uint64_t seed = o.seed >= 0 ? (uint64_t)o.seed : cfg.seed;
@@ -343,7 +347,7 @@ int run_time_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
     float *d_pc = nullptr, *d_pr = nullptr;
     size_t d_cap = 0;
     size_t frame_total = 0;
-    for (size_t fi = 0; fi < n_files; fi++) {
+    for (size_t fi = 0; fi < n_files; fi += (size_t)o.file_stride) {
         const float dur = rt_io_series_duration(main_ts.series, fi);
         const size_t frames = rt_io_frames_for_file(dur, cfg.fps, cfg.render_speed_ratio);
         // ---- scene of this file (the reference switches to this file's IAS + SBT, RendererTime.cu:420-424)
@@ -440,13 +444,14 @@ int run_mesh_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
         for (size_t k = 0; k < views[i].n_particles; k++) max_particles = std::max<size_t>(max_particles, views[i].id[k] + 1);
     }
     set_materials(scene, cfg, max_particles);
+    rs.load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - g_t0).count();
     const uint32_t spp = o.spp > 0 ? (uint32_t)o.spp : cfg.spp, depth = o.depth > 0 ? (uint32_t)o.depth : cfg.max_depth;
     const uint64_t seed = o.seed >= 0 ? (uint64_t)o.seed : cfg.seed;
     ConfigSpheres cs;
     std::vector<float> tf;
     float *d_v = nullptr, *d_n = nullptr;
     size_t cap = 0, frame_total = 0;
-    for (size_t fi = 0; fi < n_files; fi++) {
+    for (size_t fi = 0; fi < n_files; fi += (size_t)o.file_stride) {
         const rt_io_mesh_view &mv = views[fi];
         const float dur = rt_io_series_duration(series, fi);
         const size_t frames = rt_io_frames_for_file(dur, cfg.fps, cfg.render_speed_ratio);
@@ -526,13 +531,18 @@ int main(int argc, char **argv) {
     rt_camera cam;
     rt_camera_configure(cfg.camera_center, cfg.camera_target, cfg.up_direction, cfg.flip_up, &cam);  // SDL_GraphicsWindow.cu:4-14
     RunStats rs;
-    const auto t0 = std::chrono::steady_clock::now();
+    const auto t0 = g_t0 = std::chrono::steady_clock::now();
     const int rc = cfg.mesh ? run_mesh_mode(o, cfg, scene, fr, cam, st, rs) : run_time_mode(o, cfg, scene, fr, cam, st, rs);
     const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    printf("{\"frames\": %zu, \"width\": %u, \"height\": %u, \"segments\": %llu, \"build_ms\": %.3f, \"render_ms\": %.3f, "
-           "\"wall_s\": %.3f, \"mrays_per_s_render\": %.2f, \"mode\": \"%s\"}\n",
-           rs.frames, fr.w, fr.h, rs.segments, rs.build_ms, rs.render_ms, wall, rs.render_ms > 0 ? rs.segments / rs.render_ms * 1e-3 : 0.0,
-           cfg.mesh ? "mesh" : "time");
+    // frames_per_s / mrays_per_s count the frame loop (transform update + upload + rebuild + render + resolve/readback/file
+    // output as selected), not the one-off input loading
+    const double loop_s = std::max(wall - rs.load_s, 1e-9);
+    printf("{\"frames\": %zu, \"width\": %u, \"height\": %u, \"segments\": %llu, \"prims\": %llu, \"build_ms\": %.3f, \"render_ms\": %.3f, "
+           "\"wall_s\": %.3f, \"load_s\": %.3f, \"loop_s\": %.3f, \"frames_per_s\": %.3f, \"mrays_per_s\": %.2f, "
+           "\"mrays_per_s_render\": %.2f, \"build_mprims_per_s\": %.2f, \"mode\": \"%s\"}\n",
+           rs.frames, fr.w, fr.h, rs.segments, rs.prims, rs.build_ms, rs.render_ms, wall, rs.load_s, loop_s, rs.frames / loop_s,
+           rs.segments / loop_s * 1e-6, rs.render_ms > 0 ? rs.segments / rs.render_ms * 1e-3 : 0.0,
+           rs.build_ms > 0 ? rs.prims / rs.build_ms * 1e-3 : 0.0, cfg.mesh ? "mesh" : "time");
     RT(rt_scene_destroy(scene));
     rt_context_destroy(g_ctx);
     return rc;

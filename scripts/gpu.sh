@@ -9,6 +9,8 @@
 #   localmem  plain bench, then the local-memory / LSU counters of k_extend_wide
 #   buildncu  plain bench, then ncu --set full of every build kernel (one launch each)
 #   c5        C5 workload bench
+#   configs   BASELINE configs 2 and 3 at their stated size through the headless driver (needs data/ref_files/,
+#             scripts/pack_ref_data.py) + their parity tests
 #   sweep     a list of --opt settings given after the tag, one short bench each
 set -u
 JOB=${1:-check}; TAG=${2:-run}; shift 2 2>/dev/null || true
@@ -63,6 +65,24 @@ buildncu)
   ;;
 c5)
   timeout 1200 python bench.py --workload c5 --steps 4 --warmup 3 "$@" > $O/${TAG}_c5.json 2> $O/${TAG}_c5.err; echo "c5 rc=$?"; brief $O/${TAG}_c5.json; tail -2 $O/${TAG}_c5.err
+  ;;
+configs)
+  D=nvidia-optix-ray-tracer_b200/rtb200_render
+  timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -x -q > $O/${TAG}_configs_pytest.log 2>&1; echo "pytest rc=$?"; tail -2 $O/${TAG}_configs_pytest.log
+  # C2: particle.vtk.series + wall.vtk.series, all 401 files (sub-frame 0 of each), 1080p, 16 spp, depth 8, rebuild per frame
+  timeout 900 $D data/ref_files/config_c2.json --width 1920 --height 1080 --spp 16 --depth 8 --extra-series wall.vtk.series \
+      --drop-shape 3 --frame-stride 9 --format none --quiet "$@" > $O/${TAG}_c2.json 2> $O/${TAG}_c2.err; echo "c2 rc=$?"; cat $O/${TAG}_c2.json
+  # the same with one PPM per frame written (file output inside the loop)
+  timeout 900 $D data/ref_files/config_c2.json --width 1920 --height 1080 --spp 16 --depth 8 --extra-series wall.vtk.series \
+      --drop-shape 3 --frame-stride 9 --file-stride 40 --format ppm --out /tmp/${TAG}_c2_frames --quiet "$@" > $O/${TAG}_c2_ppm.json 2>> $O/${TAG}_c2.err; echo "c2 ppm rc=$?"
+  python scripts/ppm2png.py /tmp/${TAG}_c2_frames/frame_00400_000.ppm $O/${TAG}_c2_frame400.png 2
+  # C3: Mesh mode; "cache": true writes the cache files and exits (Main.cu:23-25), the second run renders from them: 4K, 64 spp, depth 5
+  sed 's/"cache": false/"cache": true/' data/ref_files/config_c3.json > data/ref_files/config_c3_cache.json
+  /usr/bin/time -f "cache generation %e s" timeout 900 $D data/ref_files/config_c3_cache.json 2> $O/${TAG}_c3.err; echo "c3 cache rc=$?"; tail -1 $O/${TAG}_c3.err
+  timeout 900 $D data/ref_files/config_c3.json --width 3840 --height 2160 --spp 64 --depth 5 --frame-stride 9 --format none --quiet "$@" \
+      > $O/${TAG}_c3.json 2>> $O/${TAG}_c3.err; echo "c3 rc=$?"; cat $O/${TAG}_c3.json
+  timeout 300 $D data/ref_files/config_c3.json --width 3840 --height 2160 --spp 64 --depth 5 --frame-stride 9 --file-stride 70 --format ppm \
+      --out /tmp/${TAG}_c3_frames --quiet "$@" > /dev/null 2>> $O/${TAG}_c3.err && python scripts/ppm2png.py /tmp/${TAG}_c3_frames/frame_00070_000.ppm $O/${TAG}_c3_frame70.png 4
   ;;
 sweep)
   # each remaining argument is one quoted option string, e.g. "--opt t1=8 --opt t2=8"
