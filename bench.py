@@ -63,6 +63,12 @@ def parse():
                          "slice only (1: measured 0.7 %% slower per frame at N=2 - the extra fence, id<->slot conversion and slice copies "
                          "cost more than half a primary pass - and it counts the primary segments once instead of N times)")
     ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
+    ap.add_argument("--shard-upload", type=int, default=1,
+                    help="N>1, e2e: each rank uploads 1/N of the (replicated) particle arrays and the slices are all-gathered over NVLink (1, default); "
+                         "0 = every rank uploads everything")
+    ap.add_argument("--pipeline-build", type=int, default=0,
+                    help="C4: 1 = two scenes, the LBVH rebuild of step i+1 runs on a second (high-priority) stream while step i "
+                         "renders (every step still rebuilds and renders once; K-1 of K rebuilds of a timed region overlap)")
     a = ap.parse_args()
     if not a.n_spheres:
         a.n_spheres = 10_000_000 if a.workload == "c4" else 100_000_000
@@ -233,9 +239,12 @@ class InputPipeline:
     """Double-buffered host -> device staging of a step's inputs on a copy stream.
     acquire(step): make the current stream wait for step's copy (issuing it now if nobody prefetched it)
     and return the device tensors to read; release(step, prefetch): the readers of that buffer have been
-    enqueued on the current stream; start copying the next step's inputs into the other buffer."""
+    enqueued on the current stream; start copying the next step's inputs into the other buffer.
+    shard = (rank, world, group): every rank needs the same arrays (replicated scene), so each rank uploads only its
+    1/world slice over PCIe and the slices are all-gathered over NVLink (NCCL, own communicator) on the copy stream —
+    the job moves the inputs across PCIe once per step instead of `world` times."""
 
-    def __init__(self, torch, pairs):
+    def __init__(self, torch, pairs, shard=None):
         self.torch = torch
         self.host = [h for h, _ in pairs]
         self.bufs = [[d for _, d in pairs], [torch.empty_like(d) for _, d in pairs]]
@@ -243,13 +252,26 @@ class InputPipeline:
         self.copied = [torch.cuda.Event(), torch.cuda.Event()]
         self.consumed = [torch.cuda.Event(), torch.cuda.Event()]
         self.pending = [None, None]  # step whose inputs are in flight / resident in buffer k
+        self.shard = shard if shard and shard[1] > 1 and all(h.numel() % shard[1] == 0 for h in self.host) else None
+        if self.shard:
+            w = self.shard[1]
+            self.stage = [torch.empty(d.numel() // w, dtype=d.dtype, device=d.device) for _, d in pairs]
+        self.h2d_bytes = sum(h.numel() * h.element_size() for h in self.host) // (self.shard[1] if self.shard else 1)
 
     def _issue(self, step):
         k = step & 1
         with self.torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[k])
-            for h, d in zip(self.host, self.bufs[k]):
-                d.copy_(h, non_blocking=True)
+            if self.shard:
+                import torch.distributed as dist
+                r, w, group = self.shard
+                for h, d, stg in zip(self.host, self.bufs[k], self.stage):
+                    m = h.numel() // w
+                    stg.copy_(h.view(-1)[r * m:(r + 1) * m], non_blocking=True)
+                    dist.all_gather_into_tensor(d.view(-1), stg, group=group)
+            else:
+                for h, d in zip(self.host, self.bufs[k]):
+                    d.copy_(h, non_blocking=True)
             self.copied[k].record(self.copy_stream)
         self.pending[k] = step
 
@@ -335,23 +357,35 @@ def run_ours(a):
     h_rgba8 = torch.zeros((npix, 4), dtype=torch.uint8).pin_memory()
 
     ctx = pkg.Context(local)
-    sc = pkg.Scene(ctx)
-    if a.leaf_max:
-        sc.set_option("leaf_max", a.leaf_max)
-    if a.batch_spp:
-        sc.set_option("batch_spp", a.batch_spp)
-    for kv in a.opt:
-        k, v = kv.split("=")
-        sc.set_option(k, int(v))
-    sc.set_option("profile", 1)
-    sc.set_materials(host["roughs"].ctypes.data, len(host["roughs"]), host["metals"].ctypes.data, len(host["metals"]))
-    g_s = sc.add_spheres(d_centers.data_ptr(), d_radii.data_ptr(), n)
-    g_w = sc.add_triangles(d_wv.data_ptr(), d_wn.data_ptr(), len(host["wall_v"]) // 3)
-    sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
-    sc.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
-    stream = torch.cuda.current_stream().cuda_stream
-    sc.build(stream)
+    stream_obj = torch.cuda.current_stream()
+    stream = stream_obj.cuda_stream
+    pipelined = bool(a.pipeline_build)
+    scs, groups = [], []
+    for _ in range(2 if pipelined else 1):
+        s_ = pkg.Scene(ctx)
+        if a.leaf_max:
+            s_.set_option("leaf_max", a.leaf_max)
+        if a.batch_spp:
+            s_.set_option("batch_spp", a.batch_spp)
+        for kv in a.opt:
+            k, v = kv.split("=")
+            s_.set_option(k, int(v))
+        s_.set_option("profile", 1)
+        s_.set_materials(host["roughs"].ctypes.data, len(host["roughs"]), host["metals"].ctypes.data, len(host["metals"]))
+        g_s = s_.add_spheres(d_centers.data_ptr(), d_radii.data_ptr(), n)
+        g_w = s_.add_triangles(d_wv.data_ptr(), d_wn.data_ptr(), len(host["wall_v"]) // 3)
+        s_.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 1, 1)   # one terrain-ramp colour per particle
+        s_.add_instance(g_w, None, pkg.RT_MAT_ROUGH, 0, 0)   # grey walls
+        s_.build(stream)
+        scs.append(s_)
+        groups.append(g_s)
+    sc = scs[0]
     scene_bytes = int(sc.stats().device_bytes)  # primitives + BVH, before any ray queue exists
+    # --pipeline-build: scene k = step & 1; its rebuild for step i+1 is enqueued on build_stream before step i's render
+    build_stream = torch.cuda.Stream(priority=-1) if pipelined else stream_obj
+    built_ev = [torch.cuda.Event() for _ in scs]
+    rendered_ev = [torch.cuda.Event() for _ in scs]
+    built_for = [None for _ in scs]
     xch = None
     if world_size > 1 and a.exchange == "peer":
         try:
@@ -362,29 +396,56 @@ def run_ours(a):
     # e2e: the particle arrays of frame i+1 travel host -> device on a copy stream while frame i renders
     # (two device buffers, rt_scene_update_group re-points the sphere group each frame; every step still
     # copies its own inputs inside the timed region, one frame ahead)
-    pipe = InputPipeline(torch, [(h_centers, d_centers), (h_radii, d_radii)])
+    shard = (rank, world_size, dist.new_group()) if world_size > 1 and a.shard_upload else None
+    pipe = InputPipeline(torch, [(h_centers, d_centers), (h_radii, d_radii)], shard)
 
-    def frame(step, e2e, prefetch=True):
-        if e2e:
-            cur = pipe.acquire(step)
-            sc.update_group(g_s, cur[0].data_ptr(), cur[1].data_ptr(), n)
-        sc.build(stream)
-        if e2e:
-            pipe.release(step, prefetch)
+    def launch_build(step, e2e, more, on):
+        """rebuild of `step` on stream `on`; `more` = a following step exists (its inputs may be prefetched)"""
+        k = step % len(scs)
+        with torch.cuda.stream(on):
+            on.wait_event(rendered_ev[k])       # the scene's previous frame has been rendered
+            if e2e:
+                cur = pipe.acquire(step)
+                scs[k].update_group(groups[k], cur[0].data_ptr(), cur[1].data_ptr(), n)
+            scs[k].build(on.cuda_stream)
+            if e2e:
+                pipe.release(step, more)
+            built_ev[k].record(on)
+        built_for[k] = step
+
+    def frame(step, e2e, ahead=2):
+        """`ahead` = how many further steps follow inside the same region (0, 1, 2+)"""
+        k = step % len(scs)
+        if built_for[k] != step:
+            launch_build(step, e2e, ahead >= 1, stream_obj)
+        stream_obj.wait_event(built_ev[k])
+        if pipelined and ahead >= 1:
+            launch_build(step + 1, e2e, ahead >= 2, build_stream)
+        cur_sc = scs[k]
+        built_for[k] = None                      # one render per rebuild
         if xch is not None:
-            mg.render_spp_split_peer(sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream,
+            mg.render_spp_split_peer(cur_sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream,
                                      split_primary=bool(a.split_primary))
+            rendered_ev[k].record(stream_obj)
             if rank == 0 and e2e:
                 h_rgba8.copy_(xch.frame, non_blocking=True)
             return
         # per-pixel XORWOW streams continue from frame to frame as in the reference (states are initialised
         # once, src/Global/RendererTime.cu:395): frame `step` owns samples [step*spp, (step+1)*spp)
-        mg.render_spp_split(sc, cam, a.width, a.height, a.spp, a.depth, a.seed, accum, frame=step, stream=stream,
+        mg.render_spp_split(cur_sc, cam, a.width, a.height, a.spp, a.depth, a.seed, accum, frame=step, stream=stream,
                             rank=rank, world=world_size)
+        rendered_ev[k].record(stream_obj)
         if rank == 0:
             ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
             if e2e:
                 h_rgba8.copy_(rgba8, non_blocking=True)
+
+    def all_stats():
+        sts = [x.stats() for x in scs]
+        return dict(segments_total=sum(int(t.segments_total) for t in sts), trace_ms=sum(float(t.trace_ms) for t in sts),
+                    trace_launches=sum(int(t.trace_launches) for t in sts), build_ms=float(np.mean([float(t.build_ms) for t in sts])),
+                    kernel_launches=sum(int(t.kernel_launches) for t in sts), device_bytes=sum(int(t.device_bytes) for t in sts),
+                    n_prims=int(sts[0].n_prims))
 
     def barrier():
         if world_size > 1:
@@ -393,32 +454,32 @@ def run_ours(a):
 
     def timed(e2e, sampler=None):
         for i in range(a.warmup):
-            frame(i, e2e, prefetch=i + 1 < a.warmup)  # the first timed step copies its own inputs, inside the region
+            frame(i, e2e, ahead=a.warmup - 1 - i)  # the first timed step copies its own inputs (and rebuilds), inside the region
         barrier()
-        st0 = sc.stats()
+        st0 = all_stats()
         if sampler:
             sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(a.steps):
-            frame(a.warmup + i, e2e, prefetch=i + 1 < a.steps)
+            frame(a.warmup + i, e2e, ahead=a.steps - 1 - i)
         pipe.drain()
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
         # segment count and per-launch traversal timings are accumulated on the device / in CUDA
         # events over the whole region and read once here (no host sync inside the region)
-        st1 = sc.stats()
-        segs = float(st1.segments_total - st0.segments_total)
-        trace_ms = float(st1.trace_ms)
-        build_ms = float(st1.build_ms)
+        st1 = all_stats()
+        segs = float(st1["segments_total"] - st0["segments_total"])
+        trace_ms = float(st1["trace_ms"])
+        build_ms = float(st1["build_ms"])
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         sg = torch.tensor([segs], device=dev, dtype=torch.float64)
         if world_size > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(sg, op=dist.ReduceOp.SUM)
         return dict(ms=float(t.item()), segs=float(sg.item()), trace_ms=trace_ms, build_ms=build_ms,
-                    launches=int(st1.kernel_launches - st0.kernel_launches), st=st1)
+                    launches=int(st1["kernel_launches"] - st0["kernel_launches"]), st=st1)
 
     sampler = ClockSampler(local) if rank == 0 else None
     dv = timed(False, sampler)
@@ -432,12 +493,12 @@ def run_ours(a):
         except OSError:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        n_prims = int(dv["st"].n_prims)
+        n_prims = int(dv["st"]["n_prims"])
         bseg = seg_bytes(n_prims)
         st = dv["st"]
         seg_step = dv["segs"] / world_size / a.steps          # this rank's segments per step
         trace_step = dv["trace_ms"] / a.steps                   # this rank's traversal-kernel time per step
-        n_launch = max(1, int(st.trace_launches))
+        n_launch = max(1, int(st["trace_launches"]))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
         traffic, traffic_src, tj, tj_note = None, None, {}, None
         try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same launch shape only)
@@ -460,15 +521,17 @@ def run_ours(a):
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
-                       "l2": "inputs larger than L2 (primitives + BVH %.0f MB; with ray queues / path state %.0f MB on the device)" % (scene_bytes / 1e6, st.device_bytes / 1e6),
-                       "step": "LBVH rebuild + render + resolve",
+                       "l2": "inputs larger than L2 (primitives + BVH %.0f MB; with ray queues / path state %.0f MB on the device)" % (scene_bytes / 1e6, st["device_bytes"] / 1e6),
+                       "step": "LBVH rebuild + render + resolve" + (" (two scenes: the rebuild of step i+1 overlaps the render of step i)" if pipelined else ""),
                        "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
                                        ("" if world_size == 1 else ("; every rank traces the whole primary pass, counted once in value (replicated copies: %.1f %% of the traced segments)"
                                                                    % (100.0 * dup / max(dv["segs"], 1.0))
                                                                    if not (xch is not None and a.split_primary) else
                                                                    "; the primary pass is split by pixel slice across the ranks"))},
             "e2e": {"value": (ee["segs"] - dup) / (ee["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ee["ms"] / a.steps,
-                    "h2d_bytes_per_step": int(h_centers.numel() * 4 + h_radii.numel() * 4) * world_size, "d2h_bytes_per_step": int(h_rgba8.numel())},
+                    "h2d_bytes_per_step": int(pipe.h2d_bytes) * world_size, "d2h_bytes_per_step": int(h_rgba8.numel()),
+                    "inputs": ("every rank uploads 1/%d of the particle arrays, NCCL all-gather over NVLink on the copy stream" % world_size) if pipe.shard
+                              else "every rank uploads the particle arrays it rebuilds from"},
             "gpu_launches": dv["launches"] * world_size,
             "clocks": clocks,
             "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
@@ -516,7 +579,7 @@ def run_ours(a):
         # correctness of the N-rank frame: one more frame through the exchange, then rank 0 renders the same samples
         # alone and compares the two RGBA8 frames (partial sums are re-associated: expect <= 1 LSB)
         fcheck = a.warmup + a.steps
-        frame(fcheck, False)
+        frame(fcheck, False, ahead=0)
         torch.cuda.synchronize()
         dist.barrier()
         if rank == 0:
@@ -531,8 +594,9 @@ def run_ours(a):
         dist.barrier()
     if rank == 0:
         if world_size == 1 and not a.no_build_100m:
-            sc.close()
-            sc = None
+            for x in scs:
+                x.close()
+            scs = []
             torch.cuda.empty_cache()
             try:
                 line["build_100m"] = build_100m(pkg, synth, torch, dev, ctx, stream, peak)
@@ -544,8 +608,8 @@ def run_ours(a):
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()
-    if sc is not None:
-        sc.close()
+    for x in scs:
+        x.close()
     ctx.close()
 
 
@@ -621,15 +685,15 @@ def run_c5(a):
 
     def timed(e2e, sampler=None):
         for i in range(a.warmup):
-            frame(i, e2e, prefetch=i + 1 < a.warmup)  # the first timed step copies its own inputs, inside the region
+            frame(i, e2e, ahead=a.warmup - 1 - i)  # the first timed step copies its own inputs (and rebuilds), inside the region
         barrier()
-        st0 = sc.stats()
+        st0 = all_stats()
         if sampler:
             sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(a.steps):
-            frame(a.warmup + i, e2e, prefetch=i + 1 < a.steps)
+            frame(a.warmup + i, e2e, ahead=a.steps - 1 - i)
         pipe.drain()
         e1.record()
         barrier()
@@ -641,7 +705,7 @@ def run_c5(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(sg, op=dist.ReduceOp.SUM)
         return dict(ms=float(t.item()), segs=float(sg.item()), trace_ms=float(st1.trace_ms), build_ms=float(st1.build_ms),
-                    launches=int(st1.kernel_launches - st0.kernel_launches), st=st1)
+                    launches=int(st1["kernel_launches"] - st0["kernel_launches"]), st=st1)
 
     sampler = ClockSampler(local) if rank == 0 else None
     dv = timed(False, sampler)
@@ -659,7 +723,7 @@ def run_c5(a):
         bseg = seg_bytes(n_prims)
         seg_step = dv["segs"] / world_size / a.steps
         trace_step = dv["trace_ms"] / a.steps
-        n_launch = max(1, int(st.trace_launches))
+        n_launch = max(1, int(st["trace_launches"]))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
         line = {
             "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,

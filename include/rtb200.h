@@ -251,7 +251,8 @@ int rt_resolve(rt_context ctx, const float *dev_accum, size_t n_pixels, float *d
  *      any may itself be peer memory, e.g. rank 0's frame buffer).  With every rank resolving its own
  *      slice this is reduce-scatter + resolve + gather in one pass over NVLink.  The caller orders
  *      the ranks (all parts complete before the call; parts not overwritten until every rank's call
- *      has finished), e.g. with a stream-ordered NCCL barrier.  n_parts <= RT_MAX_PARTS. */
+ *      has finished), e.g. with a stream-ordered NCCL barrier ENQUEUED ON THE SAME STREAM as this call and as
+ *      the rt_render that filled the part (multigpu.PeerExchange refuses any other stream).  n_parts <= RT_MAX_PARTS. */
 #define RT_MAX_PARTS 16
 #define RT_PEER_HANDLE_BYTES 64
 int rt_peer_alloc(rt_context ctx, size_t bytes, void **dev_ptr_out, unsigned char handle_out[RT_PEER_HANDLE_BYTES]);

@@ -869,8 +869,12 @@ __device__ void collapse_one(uint32_t w, int b, const Node *__restrict__ nodes, 
                 ql = fmaxf(ql - 1.0f, 0.0f);
                 qh += 1.0f;
                 if (qh > 255.0f || ql > 255.0f) {
-                    ok = false;
-                    break;
+                    if (eb[a] < 254u) {
+                        ok = false;
+                        break;
+                    }
+                    ql = 0.0f;  // largest grid and still out of range (non-finite extent): the whole axis, conservative
+                    qh = 255.0f;
                 }
                 const uint32_t sh = 8u * ((slot_of >> (4 * i)) & 7u);
                 wl |= (unsigned long long)(uint32_t)ql << sh;

@@ -273,8 +273,9 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
                 const float hi0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
                 const float lo1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), r.tmin));
                 const float hi1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
-                const bool h0 = lo0 <= hi0 * 1.000002f;
-                const bool h1 = lo1 <= hi1 * 1.000002f;
+                // an empty child (k_small_tree) keeps an inverted +-inf box, which the min/max slab test would pass
+                const bool h0 = lo0 <= hi0 * 1.000002f && n0.x <= n0.y;
+                const bool h1 = lo1 <= hi1 * 1.000002f && n1.x <= n1.y;
                 const int ch0 = __float_as_int(n3.x), ch1 = __float_as_int(n3.y);
                 if (h0 && h1) {
                     const bool swap = lo1 < lo0;
@@ -333,7 +334,13 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 //                   primitive (primitive of slot b = pbase + popc(present below b)), [31:16] pending hits.
 // The stack holds node groups only (8 bytes each).  Children are visited in octant order, which is
 // a heuristic only: every hit child is eventually visited, so the closest hit equals brute force.
+#ifdef RT_CHILD_STACK
+// per-child entries (node index, entry distance): a visit pushes at most 7, one per hit internal child it does not
+// descend into; the binary LBVH is at most 62 levels deep and a wide level consumes at least one of them
+#define RT_WSTACK (7 * 64)
+#else
 #define RT_WSTACK 64
+#endif
 // Traversal stack = shared-memory short stack + local-memory overflow.  The first RT_SH_STACK entries of a lane's
 // stack live in shared memory, laid out [entry][thread] so that the 32 lanes of a warp touch 32 consecutive
 // 8-byte words (no bank conflicts, no tag lookups, no L1 write-back traffic); deeper entries — the 8-wide tree
@@ -345,6 +352,7 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 #define RT_EXTEND_THREADS 128
 struct WideStack {
     uint2 (*sh)[RT_EXTEND_THREADS];  // [RT_SH_STACK][threads of the block]
+    float (*tl)[RT_EXTEND_THREADS];  // RT_CHILD_STACK: [8][threads] entry distances of the node under test
     uint2 ovf[RT_WSTACK - RT_SH_STACK];
     __device__ __forceinline__ void push(int sp, uint2 e) {
         if (sp < RT_SH_STACK) sh[sp][threadIdx.x] = e; else ovf[sp - RT_SH_STACK] = e;
@@ -392,6 +400,17 @@ __device__ __forceinline__ void fill_perm_table(uint8_t (*s_perm)[256]) {
     __syncthreads();
 }
 
+#ifdef RT_TRAV_STATS
+// Experiment build only (make EXTRA=-DRT_TRAV_STATS OUT=...): per-visit counters, printed by rt_scene_destroy.
+//   0 node visits, 1 visits where no valid child was hit, 2 visits whose node box (origin .. origin + 255 steps) misses
+//   [tmin, best.t], 3 the same with the tight box (min/max of the child planes), 4 primitive tests, 5 rays
+static __device__ unsigned long long g_trav_stats[8];
+__device__ __forceinline__ uint32_t bmax4(uint32_t a, uint32_t b) { return __vmaxu4(a, b); }
+__device__ __forceinline__ uint32_t bmin4(uint32_t a, uint32_t b) { return __vminu4(a, b); }
+__device__ __forceinline__ uint32_t hmax8(uint32_t a, uint32_t b) { uint32_t m = bmax4(a, b); m = bmax4(m, m >> 16); m = bmax4(m, m >> 8); return m & 255u; }
+__device__ __forceinline__ uint32_t hmin8(uint32_t a, uint32_t b) { uint32_t m = bmin4(a, b); m = bmin4(m, m >> 16); m = bmin4(m, m >> 8); return m & 255u; }
+#endif
+
 // ---- per-lane state of one closest-hit query over the 8-wide tree (kept in registers)
 struct WideTrav {
     uint32_t gbase, gmask, pbase, pmask, pbase2, pmask2;
@@ -403,6 +422,9 @@ struct WideTrav {
 };
 __device__ __forceinline__ void trav_clear(WideTrav &t) {
     t.gbase = t.gmask = t.pbase = t.pmask = t.pbase2 = t.pmask2 = 0u;
+#ifdef RT_CHILD_STACK
+    t.gbase = kNoSlot;
+#endif
     t.sp = 0;
     t.huge_done = true;
     t.huge_wait = false;
@@ -439,19 +461,42 @@ __device__ __forceinline__ void trav_start(WideTrav &t, F3 ro, F3 rd, float tmin
     t.huge_wait = false;
     t.sp = 0;
     t.pmask = t.pmask2 = 0;
+#ifdef RT_TRAV_STATS
+    atomicAdd(&g_trav_stats[5], 1ull);
+#endif
+#ifdef RT_CHILD_STACK
+    t.gbase = have_tree ? 0u : kNoSlot;  // gbase = the node to visit next (kNoSlot: take one from the stack); gmask unused
+    t.gmask = 0u;
+}
+__device__ __forceinline__ bool trav_has_nodes(const WideTrav &t) { return t.gbase != kNoSlot || t.sp > 0; }
+#else
     t.gbase = 0;
     t.gmask = have_tree ? 0x8000u : 0u;  // root: slot 7^oct of an imask-0 group -> index 0
 }
 __device__ __forceinline__ bool trav_has_nodes(const WideTrav &t) { return (t.gmask >> 8) != 0 || t.sp > 0; }
+#endif
 __device__ __forceinline__ bool trav_wants_node(const WideTrav &t) { return (t.pmask2 >> 16) == 0 && trav_has_nodes(t); }
 __device__ __forceinline__ bool trav_wants_prim(const WideTrav &t) { return (t.pmask >> 16) != 0; }
 __device__ __forceinline__ bool trav_tree_done(const WideTrav &t) { return !trav_has_nodes(t) && (t.pmask >> 16) == 0; }
+
 
 // One wide-node visit of a lane: pop the next node group entry, fetch the node (five 128-bit loads), slab-test
 // its 8 quantised child boxes, queue the hit internal children (octant order) and the hit leaf primitives.
 // `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
 __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const float4 *__restrict__ wn, uint32_t magic,
                                           const uint8_t (*s_perm)[256]) {
+#ifdef RT_CHILD_STACK
+    // per-child stack: an entry whose box is entered beyond the closest hit found since it was pushed is dropped
+    // here instead of costing a node visit (the same comparison its box test would fail now)
+    uint32_t child = t.gbase;
+    t.gbase = kNoSlot;
+    while (child == kNoSlot) {
+        if (t.sp == 0) return;
+        const uint2 e = stack.pop(--t.sp);
+        if (__uint_as_float(e.y) <= t.best.t * 1.000002f) child = e.x;
+    }
+    float tl8[8];
+#else
     if ((t.gmask >> 8) == 0) {
         const uint2 e = stack.pop(--t.sp);
         t.gbase = e.x;
@@ -462,6 +507,7 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
     const uint32_t slot = (bit - 8u) ^ t.oct;
     const uint32_t child = t.gbase + __popc(t.gmask & ((1u << slot) - 1u));
     if (t.gmask >> 8) stack.push(t.sp++, make_uint2(t.gbase, t.gmask));
+#endif
 
     const float4 *q = wn + 5 * (size_t)child;
     const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
@@ -508,12 +554,58 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
                 const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], t.tmin));
                 const float thi = fminf(fminf(tfx[e], tfy[e]), fminf(tfz[e], t.best.t));
                 if (tlo <= thi * 1.000002f) hm |= 1u << (4 * h + 2 * jp + e);  // empty slots hold an inverted box
+#ifdef RT_CHILD_STACK
+                tl8[4 * h + 2 * jp + e] = tlo;
+#endif
             }
         }
     }
     const uint32_t imask = eim >> 24, leafmask = __float_as_uint(w1.z) & 0xFFu;
+#ifdef RT_TRAV_STATS
+    {
+        atomicAdd(&g_trav_stats[0], 1ull);
+        if ((hm & (imask | leafmask)) == 0) atomicAdd(&g_trav_stats[1], 1ull);
+        const float b0x = __fmaf_rn(w0.x, t.ix, t.ox), b0y = __fmaf_rn(w0.y, t.iy, t.oy), b0z = __fmaf_rn(w0.z, t.iz, t.oz);
+        for (int tight = 0; tight < 2; tight++) {
+            float qlx = 0, qly = 0, qlz = 0, qhx = 255, qhy = 255, qhz = 255;
+            if (tight) {
+                qlx = (float)hmin8(__float_as_uint(w2.x), __float_as_uint(w2.y)); qly = (float)hmin8(__float_as_uint(w2.z), __float_as_uint(w2.w));
+                qlz = (float)hmin8(__float_as_uint(w3.x), __float_as_uint(w3.y)); qhx = (float)hmax8(__float_as_uint(w3.z), __float_as_uint(w3.w));
+                qhy = (float)hmax8(__float_as_uint(w4.x), __float_as_uint(w4.y)); qhz = (float)hmax8(__float_as_uint(w4.z), __float_as_uint(w4.w));
+            }
+            const float x0 = __fmaf_rn(qlx, sx, b0x), x1 = __fmaf_rn(qhx, sx, b0x);
+            const float y0 = __fmaf_rn(qly, sy, b0y), y1 = __fmaf_rn(qhy, sy, b0y);
+            const float z0 = __fmaf_rn(qlz, sz, b0z), z1 = __fmaf_rn(qhz, sz, b0z);
+            const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t.tmin));
+            const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t.best.t));
+            if (!(tlo <= thi * 1.000002f)) atomicAdd(&g_trav_stats[2 + tight], 1ull);
+        }
+    }
+#endif
+#ifdef RT_CHILD_STACK
+    {
+        uint32_t pr = s_perm[t.oct][hm & imask];  // bit p = the hit internal child of slot p ^ oct; higher = nearer octant
+        if (pr) {
+            const uint32_t gb = __float_as_uint(w1.x);
+            const uint32_t p0 = 31u - (uint32_t)__clz(pr);
+            pr &= ~(1u << p0);
+            if (pr) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) stack.tl[j][threadIdx.x] = tl8[j];
+                do {  // far to near, so that the nearest is popped first
+                    const uint32_t j = ((uint32_t)__ffs(pr) - 1u) ^ t.oct;
+                    pr &= pr - 1u;
+                    stack.push(t.sp++, make_uint2(gb + __popc(imask & ((1u << j) - 1u)), __float_as_uint(stack.tl[j][threadIdx.x])));
+                } while (pr);
+            }
+            const uint32_t j0 = p0 ^ t.oct;
+            t.gbase = gb + __popc(imask & ((1u << j0) - 1u));  // descend into the nearest hit child at once
+        }
+    }
+#else
     t.gbase = __float_as_uint(w1.x);
     t.gmask = imask | ((uint32_t)s_perm[t.oct][hm & imask] << 8);
+#endif
     const uint32_t pm = hm & leafmask;
     if (pm) {
         if ((t.pmask >> 16) == 0) {
@@ -530,6 +622,9 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
 __device__ __forceinline__ void trav_prim(WideTrav &t, const SceneDev &sc, F3 ro, F3 rd) {
     const uint32_t b = (uint32_t)__ffs(t.pmask >> 16) - 1u;
     t.pmask &= ~(0x10000u << b);
+#ifdef RT_TRAV_STATS
+    atomicAdd(&g_trav_stats[4], 1ull);
+#endif
     Ray r;
     r.o = ro;
     r.d = rd;
@@ -600,7 +695,8 @@ __device__ __forceinline__ bool trav_finished(const WideTrav &t) { return t.huge
 // Closest hit for a buffer of rays (wavefront form): persistent warps, dynamic ray fetch.
 __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
                                                  float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic,
-                                                 const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS]) {
+                                                 const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS],
+                                                 float (*s_tlo)[RT_EXTEND_THREADS] = nullptr) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt = (1u << lane) - 1u;
@@ -611,6 +707,7 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
 
     WideStack stack;
     stack.sh = s_stack;
+    stack.tl = s_tlo;
     WideTrav t;
     trav_clear(t);
     uint32_t idx = 0;

@@ -261,9 +261,14 @@ k_extend_wide(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint
               float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic) {
     __shared__ uint8_t s_perm[8][256];
     __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
+#ifdef RT_CHILD_STACK
+    __shared__ float s_tlo[8][RT_EXTEND_THREADS];
+#else
+    float (*s_tlo)[RT_EXTEND_THREADS] = nullptr;
+#endif
     fill_perm_table(s_perm);
     const uint32_t n = n_ptr ? *n_ptr : n_fixed;
-    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm, s_stack);
+    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_tlo);
 }
 
 // ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
@@ -474,7 +479,7 @@ struct PathArgs {
 template <bool kRefMul>
 __device__ __forceinline__ void path_warp(const SceneDev &sc, const PathArgs &a, int t1, int t2, int t3, int fetch_min, uint32_t magic,
                                           const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS],
-                                          uint32_t (*s_w)[RT_EXTEND_THREADS]) {
+                                          uint32_t (*s_w)[RT_EXTEND_THREADS], float (*s_tlo)[RT_EXTEND_THREADS] = nullptr) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u, tx = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
@@ -487,6 +492,7 @@ __device__ __forceinline__ void path_warp(const SceneDev &sc, const PathArgs &a,
 
     WideStack stack;
     stack.sh = s_stack;
+    stack.tl = s_tlo;
     WideTrav t;
     trav_clear(t);
     bool alive = false;      // the lane holds a ray whose closest hit is being searched
@@ -640,8 +646,13 @@ k_path(SceneDev sc, PathArgs a, int t1, int t2, int t3, int fetch_min, uint32_t 
     __shared__ uint8_t s_perm[8][256];
     __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
     __shared__ uint32_t s_w[kRefMul ? kPathWordsRef : kPathWords][RT_EXTEND_THREADS];
+#ifdef RT_CHILD_STACK
+    __shared__ float s_tlo[8][RT_EXTEND_THREADS];
+#else
+    float (*s_tlo)[RT_EXTEND_THREADS] = nullptr;
+#endif
     fill_perm_table(s_perm);
-    path_warp<kRefMul>(sc, a, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_w);
+    path_warp<kRefMul>(sc, a, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_w, s_tlo);
 }
 
 // Per pixel, before k_path.  Pixels whose primary ray hit something (and may scatter: max_depth > 1) are appended to
@@ -1118,6 +1129,18 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     s->last_stream = st;
     s->last_primary = n_primary;
     s->last_n_cnt = n_cnt;
+#ifdef RT_TRAV_STATS
+    {
+        unsigned long long h[8] = {0};
+        cudaDeviceSynchronize();
+        cudaMemcpyFromSymbol(h, g_trav_stats, sizeof h);
+        fprintf(stderr, "trav stats: rays %llu visits %llu (%.2f/ray) none-hit %llu (%.3f) box-miss loose %llu (%.3f) tight %llu (%.3f) prim tests %llu (%.2f/ray)\n",
+                h[5], h[0], (double)h[0] / (double)(h[5] ? h[5] : 1), h[1], (double)h[1] / (double)(h[0] ? h[0] : 1), h[2],
+                (double)h[2] / (double)(h[0] ? h[0] : 1), h[3], (double)h[3] / (double)(h[0] ? h[0] : 1), h[4], (double)h[4] / (double)(h[5] ? h[5] : 1));
+        memset(h, 0, sizeof h);
+        cudaMemcpyToSymbol(g_trav_stats, h, sizeof h);
+    }
+#endif
     return RT_OK;
 }
 

@@ -161,6 +161,14 @@ class PeerExchange:
             self.close()
             raise RuntimeError(f"peer-memory exchange unavailable on at least one rank ({err!r} on rank {rank})")
 
+    def _check_stream(self, stream):
+        """fence() and the peer copies are enqueued on torch's CURRENT stream, the kernels on `stream`: they are
+        ordered only when both are the same stream (rtb200.h, rt_resolve_parts).  Anything else would let a peer
+        read a buffer before its producer has finished: refuse it."""
+        import torch
+        if stream is not None and int(stream) != int(torch.cuda.current_stream().cuda_stream):
+            raise ValueError("PeerExchange: pass torch's current stream (or None) - the NCCL fences run on it")
+
     def fence(self):
         """Every rank's work enqueued so far is complete before anything enqueued after this runs
         (NCCL: a stream-ordered 4-byte all-reduce; other backends: device sync + host barrier)."""
@@ -177,6 +185,7 @@ class PeerExchange:
         (rt_render_primary), then copies the other slices out of the peers' buffers (NVLink reads) and
         hands the complete frame of hit records to the scene (rt_scene_set_primary_hits), so that the
         following rt_render does not repeat a pass every rank would otherwise do identically."""
+        self._check_stream(stream)
         first, cnt = pixel_slice(self.n_pixels, self.world, self.rank)
         scene.render_primary(cam, width, height, first, cnt, self.hits_ptr, stream)
         self.fence()
@@ -190,6 +199,7 @@ class PeerExchange:
 
     def resolve_slice(self, dst: int = 0, stream=None, sum_out_ptr=None):
         """Sum + resolve this rank's pixel slice from all ranks' partial sums into rank `dst`'s frame."""
+        self._check_stream(stream)
         first, cnt = pixel_slice(self.n_pixels, self.world, self.rank)
         self.fence()
         self.ctx.resolve_parts(self.parts, first, cnt, sum_out_ptr, None, self.frames[dst], stream)

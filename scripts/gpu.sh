@@ -12,6 +12,9 @@
 #   configs   BASELINE configs 2 and 3 at their stated size through the headless driver (needs data/ref_files/,
 #             scripts/pack_ref_data.py) + their parity tests
 #   sweep     a list of --opt settings given after the tag, one short bench each
+#   ab        A/B of library builds: each remaining argument is "LIBSUFFIX|bench args" (LIBSUFFIX "" = librtb200.so,
+#             "cs" = librtb200_cs.so built with make -C csrc OUT=../librtb200_cs.so EXTRA=-D...), one short bench each
+#   libtest   SUFFIX: the GPU parity tests against librtb200_SUFFIX.so
 set -u
 JOB=${1:-check}; TAG=${2:-run}; shift 2 2>/dev/null || true
 O=gpurun_out; mkdir -p $O
@@ -69,16 +72,18 @@ c5)
 configs)
   D=nvidia-optix-ray-tracer_b200/rtb200_render
   timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -x -q > $O/${TAG}_configs_pytest.log 2>&1; echo "pytest rc=$?"; tail -2 $O/${TAG}_configs_pytest.log
-  # C2: particle.vtk.series + wall.vtk.series, all 401 files (sub-frame 0 of each), 1080p, 16 spp, depth 8, rebuild per frame
+  # C2: particle.vtk.series + wall.vtk.series, all 401 files (sub-frame 0 of each), 1080p, 16 spp, depth 8, rebuild per frame;
+  # the camera-facing wall is shape 2 after the reference's transform chain (tests/test_gpu_configs.py)
   timeout 900 $D data/ref_files/config_c2.json --width 1920 --height 1080 --spp 16 --depth 8 --extra-series wall.vtk.series \
-      --drop-shape 3 --frame-stride 9 --format none --quiet "$@" > $O/${TAG}_c2.json 2> $O/${TAG}_c2.err; echo "c2 rc=$?"; cat $O/${TAG}_c2.json
+      --drop-shape 2 --frame-stride 9 --format none --quiet "$@" > $O/${TAG}_c2.json 2> $O/${TAG}_c2.err; echo "c2 rc=$?"; cat $O/${TAG}_c2.json
   # the same with one PPM per frame written (file output inside the loop)
   timeout 900 $D data/ref_files/config_c2.json --width 1920 --height 1080 --spp 16 --depth 8 --extra-series wall.vtk.series \
-      --drop-shape 3 --frame-stride 9 --file-stride 40 --format ppm --out /tmp/${TAG}_c2_frames --quiet "$@" > $O/${TAG}_c2_ppm.json 2>> $O/${TAG}_c2.err; echo "c2 ppm rc=$?"
+      --drop-shape 2 --frame-stride 9 --file-stride 40 --format ppm --out /tmp/${TAG}_c2_frames --quiet "$@" > $O/${TAG}_c2_ppm.json 2>> $O/${TAG}_c2.err; echo "c2 ppm rc=$?"
   python scripts/ppm2png.py /tmp/${TAG}_c2_frames/frame_00400_000.ppm $O/${TAG}_c2_frame400.png 2
   # C3: Mesh mode; "cache": true writes the cache files and exits (Main.cu:23-25), the second run renders from them: 4K, 64 spp, depth 5
   sed 's/"cache": false/"cache": true/' data/ref_files/config_c3.json > data/ref_files/config_c3_cache.json
-  /usr/bin/time -f "cache generation %e s" timeout 900 $D data/ref_files/config_c3_cache.json 2> $O/${TAG}_c3.err; echo "c3 cache rc=$?"; tail -1 $O/${TAG}_c3.err
+  rm -rf data/ref_files/cache; T0=$(date +%s%N)
+  timeout 900 $D data/ref_files/config_c3_cache.json 2> $O/${TAG}_c3.err; echo "c3 cache rc=$? in $(( ($(date +%s%N) - T0) / 1000000 )) ms, $(ls data/ref_files/cache | wc -l) files" | tee $O/${TAG}_c3_cache.txt; tail -1 $O/${TAG}_c3.err
   timeout 900 $D data/ref_files/config_c3.json --width 3840 --height 2160 --spp 64 --depth 5 --frame-stride 9 --format none --quiet "$@" \
       > $O/${TAG}_c3.json 2>> $O/${TAG}_c3.err; echo "c3 rc=$?"; cat $O/${TAG}_c3.json
   timeout 300 $D data/ref_files/config_c3.json --width 3840 --height 2160 --spp 64 --depth 5 --frame-stride 9 --file-stride 70 --format ppm \
@@ -92,6 +97,20 @@ sweep)
     timeout 600 python bench.py --steps 2 --warmup 2 --no-cpu-baseline $o > $O/${TAG}_s$i.json 2> $O/${TAG}_s$i.err
     echo "== [$i] $o rc=$?"; brief $O/${TAG}_s$i.json
   done
+  ;;
+ab)
+  i=0
+  for item in "$@"; do
+    i=$((i+1)); suf=${item%%|*}; args=${item#*|}
+    lib=$PWD/nvidia-optix-ray-tracer_b200/librtb200${suf:+_$suf}.so
+    RTB200_LIB=$lib timeout 600 python bench.py --steps 3 --warmup 2 --no-cpu-baseline --no-build-100m $args > $O/${TAG}_ab$i.json 2> $O/${TAG}_ab$i.err
+    echo "== [$i] lib=${suf:-default} $args rc=$?"; brief $O/${TAG}_ab$i.json
+  done
+  ;;
+libtest)
+  suf=$1
+  RTB200_LIB=$PWD/nvidia-optix-ray-tracer_b200/librtb200_$suf.so timeout 1200 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py tests/test_gpu_fused.py tests/test_gpu_build.py tests/test_gpu_refparity.py -m gpu -x -q > $O/${TAG}_libtest_$suf.log 2>&1
+  echo "libtest $suf rc=$?"; tail -3 $O/${TAG}_libtest_$suf.log
   ;;
 *) echo "unknown job $JOB"; exit 2;;
 esac

@@ -54,12 +54,16 @@ def base_scene(pkg, c, roughs):
 
 @needs_data
 def test_c2_time_series_with_walls_matches_oracle(tmp_path, pkg, hio, oracle):
-    """files/particle.vtk.series + wall.vtk.series (camera-facing wall, shape 3, dropped), rough ramp + metal ground,
-    16 spp, depth 8, BVH rebuilt per frame: files 0, 200, 400."""
+    """files/particle.vtk.series + wall.vtk.series, rough ramp + metal ground, 16 spp, depth 8, BVH rebuilt per frame:
+    files 0, 200, 400.  The camera-facing wall is dropped so that the particles are visible.  That wall is
+    shape 2, not shape 3: the wall files carry NetDEM's identity quaternion as (w, x, y, z) = (1, 0, 0, 0); the reference
+    reads the components as (x, y, z, w) (VTKReaderImpl.cpp:194-199) and its slerp returns them shifted by one place
+    (RendererTime.cu:297-340, aggregate order w, x, y, z into a float4), so every wall is turned by 180 degrees about y
+    and the x = -0.5 plane (shape 2) ends up at x = +0.5, facing the camera at (5, 0, 0).  Reproduced bit-exactly."""
     SPP, DEPTH, SEED, STRIDE = 16, 8, 7, 200
     out = str(tmp_path) + "/out"
     s = run_driver("data/ref_files/config_c2.json", out, "--spp", str(SPP), "--depth", str(DEPTH), "--seed", str(SEED),
-                   "--extra-series", "wall.vtk.series", "--drop-shape", "3", "--file-stride", str(STRIDE), "--frame-stride", "9")
+                   "--extra-series", "wall.vtk.series", "--drop-shape", "2", "--file-stride", str(STRIDE), "--frame-stride", "9")
     assert s["mode"] == "time" and s["frames"] == 3
     c = hio.load_config(os.path.join(DATA, "config_c2.json"))
     assert int(c["sphere_mat_type"][0]) == 1                      # the ground sphere is the metal
@@ -85,7 +89,7 @@ def test_c2_time_series_with_walls_matches_oracle(tmp_path, pkg, hio, oracle):
             p = hio.load_particles(sr["files"][fi])
             nxt = hio.load_particles(sr["files"][min(fi + 1, 400)])
             for k in range(len(p["id"])):
-                if int(p["shape_id"][k]) == 3:
+                if int(p["shape_id"][k]) == 2:
                     continue
                 qn = nxt["quat"][k] if k < len(nxt["id"]) else p["quat"][k]
                 t = pkg.transform_time(p["pos"][k], p["vel"][k], p["quat"][k], qn, dur, frames, 0, c["particle_shift"], c["particle_scale"])
