@@ -334,13 +334,7 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 //                   primitive (primitive of slot b = pbase + popc(present below b)), [31:16] pending hits.
 // The stack holds node groups only (8 bytes each).  Children are visited in octant order, which is
 // a heuristic only: every hit child is eventually visited, so the closest hit equals brute force.
-#ifdef RT_CHILD_STACK
-// per-child entries (node index, entry distance): a visit pushes at most 7, one per hit internal child it does not
-// descend into; the binary LBVH is at most 62 levels deep and a wide level consumes at least one of them
-#define RT_WSTACK (7 * 64)
-#else
 #define RT_WSTACK 64
-#endif
 // Traversal stack = shared-memory short stack + local-memory overflow.  The first RT_SH_STACK entries of a lane's
 // stack live in shared memory, laid out [entry][thread] so that the 32 lanes of a warp touch 32 consecutive
 // 8-byte words (no bank conflicts, no tag lookups, no L1 write-back traffic); deeper entries — the 8-wide tree
@@ -352,7 +346,6 @@ __device__ __forceinline__ void extend_warp(const SceneDev &sc, const ExtendIn &
 #define RT_EXTEND_THREADS 128
 struct WideStack {
     uint2 (*sh)[RT_EXTEND_THREADS];  // [RT_SH_STACK][threads of the block]
-    float (*tl)[RT_EXTEND_THREADS];  // RT_CHILD_STACK: [8][threads] entry distances of the node under test
     uint2 ovf[RT_WSTACK - RT_SH_STACK];
     __device__ __forceinline__ void push(int sp, uint2 e) {
         if (sp < RT_SH_STACK) sh[sp][threadIdx.x] = e; else ovf[sp - RT_SH_STACK] = e;
@@ -422,9 +415,6 @@ struct WideTrav {
 };
 __device__ __forceinline__ void trav_clear(WideTrav &t) {
     t.gbase = t.gmask = t.pbase = t.pmask = t.pbase2 = t.pmask2 = 0u;
-#ifdef RT_CHILD_STACK
-    t.gbase = kNoSlot;
-#endif
     t.sp = 0;
     t.huge_done = true;
     t.huge_wait = false;
@@ -464,17 +454,10 @@ __device__ __forceinline__ void trav_start(WideTrav &t, F3 ro, F3 rd, float tmin
 #ifdef RT_TRAV_STATS
     atomicAdd(&g_trav_stats[5], 1ull);
 #endif
-#ifdef RT_CHILD_STACK
-    t.gbase = have_tree ? 0u : kNoSlot;  // gbase = the node to visit next (kNoSlot: take one from the stack); gmask unused
-    t.gmask = 0u;
-}
-__device__ __forceinline__ bool trav_has_nodes(const WideTrav &t) { return t.gbase != kNoSlot || t.sp > 0; }
-#else
     t.gbase = 0;
     t.gmask = have_tree ? 0x8000u : 0u;  // root: slot 7^oct of an imask-0 group -> index 0
 }
 __device__ __forceinline__ bool trav_has_nodes(const WideTrav &t) { return (t.gmask >> 8) != 0 || t.sp > 0; }
-#endif
 __device__ __forceinline__ bool trav_wants_node(const WideTrav &t) { return (t.pmask2 >> 16) == 0 && trav_has_nodes(t); }
 __device__ __forceinline__ bool trav_wants_prim(const WideTrav &t) { return (t.pmask >> 16) != 0; }
 __device__ __forceinline__ bool trav_tree_done(const WideTrav &t) { return !trav_has_nodes(t) && (t.pmask >> 16) == 0; }
@@ -485,18 +468,6 @@ __device__ __forceinline__ bool trav_tree_done(const WideTrav &t) { return !trav
 // `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
 __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const float4 *__restrict__ wn, uint32_t magic,
                                           const uint8_t (*s_perm)[256]) {
-#ifdef RT_CHILD_STACK
-    // per-child stack: an entry whose box is entered beyond the closest hit found since it was pushed is dropped
-    // here instead of costing a node visit (the same comparison its box test would fail now)
-    uint32_t child = t.gbase;
-    t.gbase = kNoSlot;
-    while (child == kNoSlot) {
-        if (t.sp == 0) return;
-        const uint2 e = stack.pop(--t.sp);
-        if (__uint_as_float(e.y) <= t.best.t * 1.000002f) child = e.x;
-    }
-    float tl8[8];
-#else
     if ((t.gmask >> 8) == 0) {
         const uint2 e = stack.pop(--t.sp);
         t.gbase = e.x;
@@ -507,7 +478,6 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
     const uint32_t slot = (bit - 8u) ^ t.oct;
     const uint32_t child = t.gbase + __popc(t.gmask & ((1u << slot) - 1u));
     if (t.gmask >> 8) stack.push(t.sp++, make_uint2(t.gbase, t.gmask));
-#endif
 
     const float4 *q = wn + 5 * (size_t)child;
     const float4 w0 = ldg4(q), w1 = ldg4(q + 1), w2 = ldg4(q + 2), w3 = ldg4(q + 3), w4 = ldg4(q + 4);
@@ -554,9 +524,6 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
                 const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], t.tmin));
                 const float thi = fminf(fminf(tfx[e], tfy[e]), fminf(tfz[e], t.best.t));
                 if (tlo <= thi * 1.000002f) hm |= 1u << (4 * h + 2 * jp + e);  // empty slots hold an inverted box
-#ifdef RT_CHILD_STACK
-                tl8[4 * h + 2 * jp + e] = tlo;
-#endif
             }
         }
     }
@@ -582,30 +549,8 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
         }
     }
 #endif
-#ifdef RT_CHILD_STACK
-    {
-        uint32_t pr = s_perm[t.oct][hm & imask];  // bit p = the hit internal child of slot p ^ oct; higher = nearer octant
-        if (pr) {
-            const uint32_t gb = __float_as_uint(w1.x);
-            const uint32_t p0 = 31u - (uint32_t)__clz(pr);
-            pr &= ~(1u << p0);
-            if (pr) {
-#pragma unroll
-                for (int j = 0; j < 8; j++) stack.tl[j][threadIdx.x] = tl8[j];
-                do {  // far to near, so that the nearest is popped first
-                    const uint32_t j = ((uint32_t)__ffs(pr) - 1u) ^ t.oct;
-                    pr &= pr - 1u;
-                    stack.push(t.sp++, make_uint2(gb + __popc(imask & ((1u << j) - 1u)), __float_as_uint(stack.tl[j][threadIdx.x])));
-                } while (pr);
-            }
-            const uint32_t j0 = p0 ^ t.oct;
-            t.gbase = gb + __popc(imask & ((1u << j0) - 1u));  // descend into the nearest hit child at once
-        }
-    }
-#else
     t.gbase = __float_as_uint(w1.x);
     t.gmask = imask | ((uint32_t)s_perm[t.oct][hm & imask] << 8);
-#endif
     const uint32_t pm = hm & leafmask;
     if (pm) {
         if ((t.pmask >> 16) == 0) {
@@ -695,8 +640,7 @@ __device__ __forceinline__ bool trav_finished(const WideTrav &t) { return t.huge
 // Closest hit for a buffer of rays (wavefront form): persistent warps, dynamic ray fetch.
 __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const ExtendIn &in, uint32_t n, uint32_t *fetch_ctr,
                                                  float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic,
-                                                 const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS],
-                                                 float (*s_tlo)[RT_EXTEND_THREADS] = nullptr) {
+                                                 const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS]) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lt = (1u << lane) - 1u;
@@ -707,7 +651,6 @@ __device__ __forceinline__ void extend_warp_wide(const SceneDev &sc, const Exten
 
     WideStack stack;
     stack.sh = s_stack;
-    stack.tl = s_tlo;
     WideTrav t;
     trav_clear(t);
     uint32_t idx = 0;

@@ -261,14 +261,9 @@ k_extend_wide(SceneDev sc, ExtendIn in, const uint32_t *__restrict__ n_ptr, uint
               float4 *__restrict__ hits, int t1, int t2, int t3, int fetch_min, uint32_t magic) {
     __shared__ uint8_t s_perm[8][256];
     __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
-#ifdef RT_CHILD_STACK
-    __shared__ float s_tlo[8][RT_EXTEND_THREADS];
-#else
-    float (*s_tlo)[RT_EXTEND_THREADS] = nullptr;
-#endif
     fill_perm_table(s_perm);
     const uint32_t n = n_ptr ? *n_ptr : n_fixed;
-    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_tlo);
+    extend_warp_wide(sc, in, n, fetch_ctr, hits, t1, t2, t3, fetch_min, magic, s_perm, s_stack);
 }
 
 // ------------------------------------------------------------------ primary rays (raygen, Shader.cu:246-267)
@@ -479,7 +474,7 @@ struct PathArgs {
 template <bool kRefMul>
 __device__ __forceinline__ void path_warp(const SceneDev &sc, const PathArgs &a, int t1, int t2, int t3, int fetch_min, uint32_t magic,
                                           const uint8_t (*s_perm)[256], uint2 (*s_stack)[RT_EXTEND_THREADS],
-                                          uint32_t (*s_w)[RT_EXTEND_THREADS], float (*s_tlo)[RT_EXTEND_THREADS] = nullptr) {
+                                          uint32_t (*s_w)[RT_EXTEND_THREADS]) {
     const uint32_t FULL = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u, tx = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
@@ -492,7 +487,6 @@ __device__ __forceinline__ void path_warp(const SceneDev &sc, const PathArgs &a,
 
     WideStack stack;
     stack.sh = s_stack;
-    stack.tl = s_tlo;
     WideTrav t;
     trav_clear(t);
     bool alive = false;      // the lane holds a ray whose closest hit is being searched
@@ -646,13 +640,8 @@ k_path(SceneDev sc, PathArgs a, int t1, int t2, int t3, int fetch_min, uint32_t 
     __shared__ uint8_t s_perm[8][256];
     __shared__ uint2 s_stack[RT_SH_STACK][RT_EXTEND_THREADS];
     __shared__ uint32_t s_w[kRefMul ? kPathWordsRef : kPathWords][RT_EXTEND_THREADS];
-#ifdef RT_CHILD_STACK
-    __shared__ float s_tlo[8][RT_EXTEND_THREADS];
-#else
-    float (*s_tlo)[RT_EXTEND_THREADS] = nullptr;
-#endif
     fill_perm_table(s_perm);
-    path_warp<kRefMul>(sc, a, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_w, s_tlo);
+    path_warp<kRefMul>(sc, a, t1, t2, t3, fetch_min, magic, s_perm, s_stack, s_w);
 }
 
 // Per pixel, before k_path.  Pixels whose primary ray hit something (and may scatter: max_depth > 1) are appended to
