@@ -135,7 +135,8 @@ struct DevBuf {  // grow-only device buffer
 struct Context {
     int device = 0;
     int sm_count = 148;
-    int collapse_blocks = 0;  // co-resident grid of the cooperative collapse kernel
+    int collapse_blocks = 0;  // co-resident grid of the cooperative collapse kernel (one thread per wide node)
+    int collapse8_blocks = 0; // the same for k_collapse8 (eight lanes per wide node)
     std::mutex mu;
     std::string last_error;
 };
@@ -218,6 +219,7 @@ struct Scene {
     uint32_t t1 = 16, t2 = 4, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
     uint32_t extend_blocks_per_sm = 7;
     uint32_t ray_bins = 8, shade_threads = 512;  // queue grouping of scattered rays (rt_render.cu binned_push)
+    uint32_t collapse_mode = 0;   // 0: k_collapse (one thread per wide node); 1: k_collapse8 (eight lanes per wide node)
     uint32_t refit_mode = 1;      // 0: one kernel, global counters; 1: k_refit_local (shared memory) + k_refit_top
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;

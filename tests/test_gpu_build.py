@@ -201,6 +201,21 @@ def test_wide_tree_invariants(pkg, synth, n, ntri, ground, refit_mode):
     gs.close()
 
 
+@pytest.mark.parametrize("n,ntri,ground", [(1, 0, False), (5, 3, False), (1000, 200, True), (30000, 0, False)])
+def test_wide_tree_group_collapse(pkg, synth, oracle, n, ntri, ground):
+    """option collapse_mode = 1 (k_collapse8: eight lanes per wide node, all internal children opened per round):
+    another valid 8-wide tree over the same primitives — same invariants, same image bit for bit."""
+    d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
+    world = scenes.flatten_world(d)
+    gs = scenes.GpuScene(pkg, d, options={"collapse_mode": 1})
+    check_wide_tree(gs, world)
+    cam = scenes.config_camera(pkg, "VK")
+    g = gs.render(cam, 96, 64, 2, 5, 5)
+    o = oracle.render(world, cam, 96, 64, 2, 5, 5, accel=1)
+    assert np.array_equal(g["prim_id"], o["prim_id"]) and np.array_equal(g["accum"].view(np.uint32), o["accum"].view(np.uint32))
+    gs.close()
+
+
 def test_wide_tree_duplicate_keys(pkg):
     c = np.zeros((300, 3), np.float32)
     c[:200] = [0.1, 0.1, 0.1]
