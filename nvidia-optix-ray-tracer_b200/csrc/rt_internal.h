@@ -136,6 +136,7 @@ struct Context {
     int device = 0;
     int sm_count = 148;
     int collapse_blocks = 0;  // co-resident grid of the cooperative collapse kernel (one thread per wide node)
+    bool rmq_attr_set = false;  // k_refit_rmq's dynamic shared memory limit has been raised
     int collapse8_blocks = 0; // the same for k_collapse8 (eight lanes per wide node)
     std::mutex mu;
     std::string last_error;
@@ -220,7 +221,7 @@ struct Scene {
     uint32_t extend_blocks_per_sm = 7;
     uint32_t ray_bins = 8, shade_threads = 512;  // queue grouping of scattered rays (rt_render.cu binned_push)
     uint32_t collapse_mode = 0;   // 0: k_collapse (one thread per wide node); 1: k_collapse8 (eight lanes per wide node)
-    uint32_t refit_mode = 1;      // 0: one kernel, global counters; 1: k_refit_local (shared memory) + k_refit_top
+    uint32_t refit_mode = 1;      // 0: one kernel, global counters; 1: k_refit_local (shared-memory climb) + k_refit_top; 2: k_refit_rmq (range queries) + k_refit_top
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;
 

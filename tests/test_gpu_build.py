@@ -71,7 +71,7 @@ def check_tree(st, nodes, prim, keys, world):
 
 
 @pytest.mark.parametrize("n,ntri,ground", [(2, 0, False), (5, 3, False), (64, 16, True), (1000, 200, True), (50000, 0, False)])
-@pytest.mark.parametrize("refit_mode", [0, 1])
+@pytest.mark.parametrize("refit_mode", [0, 1, 2])
 def test_tree_invariants(pkg, synth, n, ntri, ground, refit_mode):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
     world = scenes.flatten_world(d)
@@ -190,7 +190,7 @@ def check_wide_tree(gs, world):
 
 
 @pytest.mark.parametrize("n,ntri,ground", [(1, 0, False), (2, 0, False), (5, 3, False), (64, 16, True), (1000, 200, True), (30000, 0, False)])
-@pytest.mark.parametrize("refit_mode", [0, 1])
+@pytest.mark.parametrize("refit_mode", [0, 1, 2])
 def test_wide_tree_invariants(pkg, synth, n, ntri, ground, refit_mode):
     d = scenes.random_scene(pkg, synth, n, n_tris=ntri, seed=n, with_walls=n >= 64, with_ground=ground)
     world = scenes.flatten_world(d)
