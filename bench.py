@@ -63,6 +63,10 @@ def parse():
                          "slice only (1: measured 0.7 %% slower per frame at N=2 - the extra fence, id<->slot conversion and slice copies "
                          "cost more than half a primary pass - and it counts the primary segments once instead of N times)")
     ap.add_argument("--opt", action="append", default=[], help="scene option name=value (tuning), repeatable")
+    ap.add_argument("--stream-layout", default="rank", choices=["rank", "frame"],
+                    help="N>1: which samples of the per-pixel streams a rank renders (multigpu.frame_sample_offset): 'rank' = its own "
+                         "contiguous region, no per-frame re-positioning of the RNG states (default); 'frame' = a slice of the block a "
+                         "single GPU would render for that frame")
     ap.add_argument("--shard-upload", type=int, default=1,
                     help="N>1, e2e: each rank uploads 1/N of the (replicated) particle arrays and the slices are all-gathered over NVLink (1, default); "
                          "0 = every rank uploads everything")
@@ -425,7 +429,7 @@ def run_ours(a):
         built_for[k] = None                      # one render per rebuild
         if xch is not None:
             mg.render_spp_split_peer(cur_sc, xch, cam, a.width, a.height, a.spp, a.depth, a.seed, frame=step, stream=stream,
-                                     split_primary=bool(a.split_primary))
+                                     split_primary=bool(a.split_primary), layout=a.stream_layout)
             rendered_ev[k].record(stream_obj)
             if rank == 0 and e2e:
                 h_rgba8.copy_(xch.frame, non_blocking=True)
@@ -433,7 +437,7 @@ def run_ours(a):
         # per-pixel XORWOW streams continue from frame to frame as in the reference (states are initialised
         # once, src/Global/RendererTime.cu:395): frame `step` owns samples [step*spp, (step+1)*spp)
         mg.render_spp_split(cur_sc, cam, a.width, a.height, a.spp, a.depth, a.seed, accum, frame=step, stream=stream,
-                            rank=rank, world=world_size)
+                            rank=rank, world=world_size, layout=a.stream_layout)
         rendered_ev[k].record(stream_obj)
         if rank == 0:
             ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
@@ -522,6 +526,9 @@ def run_ours(a):
             "config": {"workload": workload_name(a), "parallelism": (f"spp-split x{world_size} + " + ("peer-memory slice sum+resolve kernel (reduce-scatter+resolve+gather over NVLink)" + (", primary visibility split by pixel slice" if a.split_primary else "")
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (primitives + BVH %.0f MB; with ray queues / path state %.0f MB on the device)" % (scene_bytes / 1e6, st["device_bytes"] / 1e6),
+                       "streams": ("single rank: frame f = samples [f*spp, (f+1)*spp) of every pixel's stream" if world_size == 1 else
+                                   ("rank r walks its own region of every pixel's stream (no per-frame re-positioning)" if a.stream_layout == "rank"
+                                    else "frame f = samples [f*spp, (f+1)*spp), split over the ranks (states re-positioned every frame)")),
                        "step": "LBVH rebuild + render + resolve" + (" (two scenes: the rebuild of step i+1 overlaps the render of step i)" if pipelined else ""),
                        "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
                                        ("" if world_size == 1 else ("; every rank traces the whole primary pass, counted once in value (replicated copies: %.1f %% of the traced segments)"
@@ -585,11 +592,15 @@ def run_ours(a):
         if rank == 0:
             multi = (xch.frame if xch is not None else rgba8).clone()
             sc.build(stream)
-            sc.render(cam, a.width, a.height, a.spp, a.depth, a.seed, (0.7, 0.8, 0.9), fcheck * a.spp, 0, accum.data_ptr(), None, None, None, stream)
+            for r in range(world_size):  # the same sample blocks, one after the other, accumulated in rank order
+                off, cnt = mg.frame_sample_offset(fcheck, a.spp, world_size, r, a.stream_layout)
+                if cnt:
+                    sc.render(cam, a.width, a.height, cnt, a.depth, a.seed, (0.7, 0.8, 0.9), off, pkg.RT_FLAG_ACCUMULATE if r else 0,
+                              accum.data_ptr(), None, None, None, stream)
             ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
             torch.cuda.synchronize()
             diff = (multi.to(torch.int16) - rgba8.to(torch.int16)).abs()
-            line["parity_check"] = {"against": "the same frame rendered by rank 0 alone", "pixels": npix,
+            line["parity_check"] = {"against": "the same sample blocks rendered by rank 0 alone", "pixels": npix, "stream_layout": a.stream_layout,
                                     "rgba8_max_abs_diff": int(diff.max().item()), "rgba8_pixels_differing": int((diff.amax(dim=1) > 0).sum().item())}
         dist.barrier()
     if rank == 0:

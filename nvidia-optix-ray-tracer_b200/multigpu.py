@@ -6,7 +6,9 @@ single-GPU, docs/technical-details.md:327).  One process per GPU, `torch.distrib
                  a sum-reduce of the float4 accumulation buffer to rank 0 (NCCL over NVLink on the
                  GPU box, gloo in the CPU tests).  Sample s of pixel p uses the same XORWOW stream
                  (seed, p, s*32) whatever the partition, so the image does not depend on the world
-                 size except for the fp32 re-association of the per-rank partial sums.
+                 size except for the fp32 re-association of the per-rank partial sums (layout "frame";
+                 layout "rank" gives every rank its own contiguous region of the streams instead,
+                 which spares the per-frame re-positioning of the RNG states: frame_sample_offset).
   frame parallel frame f of a time series goes to rank f mod world; no collective on the data path.
 
 Nothing here computes pixels: rendering goes through the C ABI (Scene.render)."""
@@ -33,11 +35,27 @@ def spp_partition(spp: int, world: int, rank: int) -> Tuple[int, int]:
     return offset, count
 
 
-def frame_sample_offset(frame: int, spp: int, world: int, rank: int) -> Tuple[int, int]:
+RANK_REGION = 1 << 20  # samples of a pixel's stream reserved per rank by the "rank" layout (2^25 draws of the 2^67 a sequence holds)
+
+
+def frame_sample_offset(frame: int, spp: int, world: int, rank: int, layout: str = "frame") -> Tuple[int, int]:
     """Sample block of `rank` for frame `frame` when the per-pixel streams continue across frames
     (the reference initialises its RNG states once and keeps consuming them frame after frame,
-    src/Global/RendererTime.cu:395 + shader/Shader.cu:170): frame f owns samples [f*spp, (f+1)*spp)."""
+    src/Global/RendererTime.cu:395 + shader/Shader.cu:170).
+      layout "frame": frame f owns samples [f*spp, (f+1)*spp) and the ranks split that block — the frame is the one a
+                      single GPU renders, whatever the world size (partial sums re-associated), but from one frame to
+                      the next a rank's block is not contiguous: its per-pixel states are re-positioned every frame
+                      (one GF(2) matrix-vector product per pixel, ~1 ms at 4K).
+      layout "rank":  rank r owns the region [r*RANK_REGION, (r+1)*RANK_REGION) of every pixel's stream and walks it
+                      contiguously, frame after frame: no re-positioning.  The frame then is the sum of `world`
+                      single-GPU renders at those offsets (same estimator, disjoint samples)."""
     off, cnt = spp_partition(spp, world, rank)
+    if layout == "rank":
+        if (frame + 1) * cnt > RANK_REGION:
+            raise ValueError("rank layout: a rank's region of the sample stream is exhausted")
+        return rank * RANK_REGION + frame * cnt, cnt
+    if layout != "frame":
+        raise ValueError(f"unknown layout {layout!r}")
     return frame * spp + off, cnt
 
 
@@ -59,7 +77,7 @@ def reduce_accum(accum, dst: int = 0):
 
 def render_spp_split(scene, cam, width, height, spp, max_depth, seed, accum, *, frame: int = 0,
                      background=(0.7, 0.8, 0.9), stream=None, rank: int | None = None,
-                     world: int | None = None, dst: int = 0):
+                     world: int | None = None, dst: int = 0, layout: str = "frame"):
     """One frame of the spp-split path on this rank: render this rank's sample block into `accum`
     (a torch float32 tensor [w*h, 4] on the rank's GPU) and reduce to `dst`.  Returns the number of
     samples this rank rendered."""
@@ -67,7 +85,7 @@ def render_spp_split(scene, cam, width, height, spp, max_depth, seed, accum, *, 
         r, _, w = env_world()
         rank = r if rank is None else rank
         world = w if world is None else world
-    off, cnt = frame_sample_offset(frame, spp, world, rank)
+    off, cnt = frame_sample_offset(frame, spp, world, rank, layout)
     if cnt:
         scene.render(cam, width, height, cnt, max_depth, seed, background, off, 0, accum.data_ptr(), None, None,
                      None, stream)
@@ -223,10 +241,11 @@ class PeerExchange:
 
 
 def render_spp_split_peer(scene, xch: PeerExchange, cam, width, height, spp, max_depth, seed, *, frame: int = 0,
-                          background=(0.7, 0.8, 0.9), stream=None, dst: int = 0, split_primary: bool = False):
+                          background=(0.7, 0.8, 0.9), stream=None, dst: int = 0, split_primary: bool = False,
+                          layout: str = "frame"):
     """One frame of the spp split with the peer-memory exchange: this rank's sample block goes into its
     own exchange buffer, then every rank sums and resolves its pixel slice into rank `dst`'s RGBA8 frame."""
-    off, cnt = frame_sample_offset(frame, spp, xch.world, xch.rank)
+    off, cnt = frame_sample_offset(frame, spp, xch.world, xch.rank, layout)
     split = split_primary and xch.world > 1
     if split:
         xch.gather_primary(scene, cam, width, height, stream)

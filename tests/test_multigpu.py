@@ -29,6 +29,17 @@ def test_spp_partition_covers_every_sample_once():
                 seen += list(range(off, off + cnt))
             assert seen == list(range(spp)), (spp, world)
     assert mg.frame_sample_offset(3, 64, 8, 2) == (3 * 64 + 16, 8)
+    # "rank" layout: every rank walks its own region contiguously from frame to frame; all blocks disjoint
+    seen = set()
+    for frame in range(3):
+        for r in range(4):
+            off, cnt = mg.frame_sample_offset(frame, 10, 4, r, "rank")
+            assert off == r * mg.RANK_REGION + frame * cnt and cnt == (3 if r < 2 else 2)
+            blk = set(range(off, off + cnt))
+            assert not (blk & seen)
+            seen |= blk
+    with pytest.raises(ValueError):
+        mg.frame_sample_offset(0, 8, 2, 0, "tile")
     with pytest.raises(ValueError):
         mg.spp_partition(8, 2, 2)
 
