@@ -150,7 +150,7 @@ int rt_scene_destroy(rt_scene scene) {
     s.sort_hist.release(); s.bucket_tab.release(); s.nodes.release(); s.parent_int.release(); s.parent_leaf.release();
     s.visit.release(); s.slot_geom.release(); s.slot_prim.release(); s.slot_mat.release(); s.info.release();
     s.wnodes.release(); s.wslot_geom.release(); s.wslot_prim.release(); s.wslot_mat.release();
-    s.phit.release(); s.hit.release(); s.u_skip.release(); s.prim_fetch.release(); s.rng_base.release(); s.rng_cur.release(); s.result.release(); s.hit_pix.release(); s.rng_start.release(); s.rng_pix_off.release(); s.counters.release(); s.seg_total.release();
+    s.phit.release(); s.hit.release(); s.u_skip.release(); s.prim_fetch.release(); s.rng_cur.release(); s.result.release(); s.hit_pix.release(); s.rng_start.release(); s.rng_pix_off.release(); s.counters.release(); s.seg_total.release();
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);

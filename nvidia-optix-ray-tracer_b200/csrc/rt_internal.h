@@ -196,11 +196,10 @@ struct Scene {
 
     // render
     DevBuf<float4> phit;          // per pixel: t, bits(slot), u, v
-    DevBuf<uint32_t> rng_base;    // 6 words per pixel (pristine) SoA: [6][npix]
-    DevBuf<uint32_t> rng_cur;     // working copy
+    DevBuf<uint32_t> rng_cur;     // XORWOW state per pixel, 6 words SoA: [6][npix]; pixel p stands at sample rng_pix_off[p]
     uint64_t rng_seed = 0;
-    uint32_t rng_w = 0, rng_h = 0, rng_off = 0;  // key of rng_base
-    uint64_t rng_cur_off = ~0ull;                // sample offset rng_cur currently sits at
+    uint32_t rng_w = 0, rng_h = 0;               // (seed, size) the states belong to
+    uint64_t rng_cur_off = ~0ull;                // sample offset after the last launch (what an up-to-date pixel stands at)
     bool rng_valid = false;
     DevBuf<float4> q_o[2], q_d[2], q_t[2];
     DevBuf<uint4> q_r[2];
@@ -209,8 +208,7 @@ struct Scene {
     DevBuf<float4> result;        // per path
     DevBuf<uint32_t> hit_pix;     // fused form: pixels whose primary ray hit something
     DevBuf<uint32_t> rng_start;   // fused form: [sample][6][npix] XORWOW state of stream(p, s) per hit pixel
-    DevBuf<uint32_t> rng_pix_off; // fused form: sample offset the state of pixel p in rng_cur stands at (lazy stepping)
-    bool rng_lazy = false;        // rng_cur / rng_off were last written by the fused form
+    DevBuf<uint32_t> rng_pix_off; // sample offset the state of pixel p in rng_cur stands at (lazy stepping: only pixels that hit draw)
     bool fused = false;           // option "fused": one persistent path kernel instead of per-bounce wavefront launches
     uint32_t chunk_spp = 16;      // option "chunk_spp": samples per work unit of the fused kernel
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)

@@ -63,8 +63,10 @@ __device__ __forceinline__ Ray primary_ray(const CamDev &cam, uint32_t x, uint32
 // exact: the states are bit-identical to curand_init(seed, p, offset) (checked against the oracle,
 // which calls the real thing per pixel).  d (the Weyl counter) depends on seed and offset only.
 constexpr uint32_t kRngRun = 64;
+constexpr uint32_t kRngMaxLag = 2048;  // samples; beyond it curand_init (sequence skip by matrices) is cheaper than stepping
 __global__ void __launch_bounds__(128)
-k_rng_init(uint32_t *__restrict__ rng, uint32_t npix, unsigned long long seed, unsigned long long offset) {
+k_rng_init(uint32_t *__restrict__ rng, uint32_t *__restrict__ rng_off, uint32_t off_samples, uint32_t npix, unsigned long long seed,
+           unsigned long long offset) {
     __shared__ uint4 s_row[160][2];  // row i of S padded to 8 words: one 128-bit + one 32-bit shared load
     for (uint32_t i = threadIdx.x; i < 160; i += blockDim.x) {
         const unsigned int *m = &precalc_xorwow_matrix[0][5 * i];
@@ -85,6 +87,7 @@ k_rng_init(uint32_t *__restrict__ rng, uint32_t npix, unsigned long long seed, u
         rng[3 * (size_t)npix + p] = v[2];
         rng[4 * (size_t)npix + p] = v[3];
         rng[5 * (size_t)npix + p] = v[4];
+        rng_off[p] = off_samples;  // the sample this pixel's state stands at (states advance lazily, per pixel)
         if (p + 1 == end) break;
         uint32_t y0 = 0, y1 = 0, y2 = 0, y3 = 0, y4 = 0;
 #pragma unroll
@@ -314,8 +317,8 @@ k_primary_aov(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, const float4 *__r
 constexpr int kPrimaryThreads = 512;
 __global__ void __launch_bounds__(kPrimaryThreads)
 k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
-                const float4 *__restrict__ phit, uint32_t *__restrict__ rng, Queue out, uint32_t *out_count,
-                float4 *__restrict__ result, uint32_t nb, uint32_t flags) {
+                const float4 *__restrict__ phit, uint32_t *__restrict__ rng, uint32_t *__restrict__ rng_off, unsigned long long seed,
+                uint32_t sample_offset, Queue out, uint32_t *out_count, float4 *__restrict__ result, uint32_t nb, uint32_t flags) {
     __shared__ uint32_t s_cnt[kPrimaryThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     uint32_t x, y;
@@ -333,15 +336,28 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
         hit.slot = __float_as_uint(h.y);
         hit.u = h.z;
         hit.v = h.w;
-        st.d = rng[0 * (size_t)npix + p];
-        st.v0 = rng[1 * (size_t)npix + p];
-        st.v1 = rng[2 * (size_t)npix + p];
-        st.v2 = rng[3 * (size_t)npix + p];
-        st.v3 = rng[4 * (size_t)npix + p];
-        st.v4 = rng[5 * (size_t)npix + p];
     }
     const bool is_hit = valid && hit.slot != kNoSlot;
     const bool go = is_hit && max_depth > 1u;  // Shader.cu:102-107 with depth == 1
+    // Only pixels that continue a path draw random numbers, so only their streams are touched: a pixel's state is
+    // advanced lazily, from the sample it stands at (rng_off) to this launch's first sample, when the pixel needs it
+    // (C4: 76 % of the pixels miss; stepping every pixel's stream by S * 32 draws was a third of this kernel).
+    if (go) {
+        const uint32_t have = rng_off[p];
+        if (have > sample_offset || sample_offset - have > kRngMaxLag) {
+            curandStateXORWOW cs;
+            curand_init(seed, (unsigned long long)p, (unsigned long long)sample_offset * RT_RNG_SAMPLE_STRIDE, &cs);
+            st.d = cs.d; st.v0 = cs.v[0]; st.v1 = cs.v[1]; st.v2 = cs.v[2]; st.v3 = cs.v[3]; st.v4 = cs.v[4];
+        } else {
+            st.d = rng[0 * (size_t)npix + p];
+            st.v0 = rng[1 * (size_t)npix + p];
+            st.v1 = rng[2 * (size_t)npix + p];
+            st.v2 = rng[3 * (size_t)npix + p];
+            st.v3 = rng[4 * (size_t)npix + p];
+            st.v4 = rng[5 * (size_t)npix + p];
+            for (uint32_t k = (sample_offset - have) * RT_RNG_SAMPLE_STRIDE; k > 0; k--) (void)rng_next(st);
+        }
+    }
     for (uint32_t s = 0; s < S; s++) {
         const size_t pid = (size_t)p * S + s;
         Scatter sc1;
@@ -356,12 +372,13 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
             // miss: 1 * background (Shader.cu:276-287); depth cut-off: 0 (:102-107)
             result[pid] = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
         }
-        if (valid) {  // every pixel's stream advances (a pixel that misses now may hit after the next rebuild)
+        if (go) {
 #pragma unroll 8
             for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
         }
     }
-    if (valid) {
+    if (go) {
+        rng_off[p] = sample_offset + S;
         rng[0 * (size_t)npix + p] = st.d;
         rng[1 * (size_t)npix + p] = st.v0;
         rng[2 * (size_t)npix + p] = st.v1;
@@ -652,7 +669,6 @@ k_path(SceneDev sc, PathArgs a, int t1, int t2, int t3, int fetch_min, uint32_t 
 // at, and a pixel that starts to hit after a rebuild catches up first (or is re-initialised when it lags far).
 // The list order is block-ordered (tile order inside a block): neighbouring lanes of k_path work on neighbouring pixels.
 constexpr int kPrepThreads = 256;
-constexpr uint32_t kRngMaxLag = 2048;  // samples; beyond it curand_init (sequence skip by matrices) is cheaper than stepping
 __global__ void __launch_bounds__(kPrepThreads)
 k_prepare(uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg, const float4 *__restrict__ phit, uint32_t *__restrict__ rng,
           uint32_t *__restrict__ rng_off, unsigned long long seed, uint32_t sample_offset, uint32_t *__restrict__ hit_pix,
@@ -949,8 +965,8 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         RT_CUDA(ctx, s->rng_start.reserve((size_t)std::min(Sb, spp) * 6 * npix, &s->bytes));
         RT_CUDA(ctx, s->result.reserve((size_t)npix * std::min(Sb, spp), &s->bytes));
     } else if (spp) {
-        RT_CUDA(ctx, s->rng_base.reserve(6 * (size_t)npix, &s->bytes));
         RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
+        RT_CUDA(ctx, s->rng_pix_off.reserve(npix, &s->bytes));
         for (int k = 0; k < 2; k++) {
             RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
             RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
@@ -991,21 +1007,13 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     // (re)positioned (first frame, or a rank of the spp split whose sample blocks are not contiguous from
     // frame to frame) that runs on a side stream next to the primary-visibility pass, which does not need them.
     bool rng_forked = false;
-    if (spp && fused) {
-        // lazy per-pixel streams (k_prepare): a state is (re)created on demand, so a new seed / size / form only has
-        // to mark every pixel's state as absent
-        const bool ok = s->rng_valid && s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H;
-        if (!ok) {
-            RT_CUDA(ctx, cudaMemsetAsync(s->rng_pix_off.p, 0xFF, (size_t)npix * sizeof(uint32_t), st));
-            s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H;
-            s->rng_valid = true;
-            s->rng_lazy = true;
-        }
-    } else if (spp) {
-        const bool base_ok = s->rng_valid && !s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H && s->rng_off == fp->sample_offset;
-        const bool cont_ok = s->rng_valid && !s->rng_lazy && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H &&
-                             s->rng_cur_off == (uint64_t)fp->sample_offset;
-        if (!cont_ok) {
+    if (spp) {
+        // Both forms keep one state per pixel (rng_cur) plus the sample it stands at (rng_pix_off) and advance it lazily.
+        // A new seed / size, a request behind the states or far ahead of them re-creates all of them at this launch's
+        // first sample (k_rng_init, ~1 ms at 4K) rather than leaving it to the per-pixel curand_init of the kernels.
+        const bool same = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H;
+        const bool reinit = !same || (uint64_t)fp->sample_offset < s->rng_cur_off || (uint64_t)fp->sample_offset - s->rng_cur_off > kRngMaxLag;
+        if (reinit) {
             if (!s->aux_stream) {
                 RT_CUDA(ctx, cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
                 RT_CUDA(ctx, cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
@@ -1013,15 +1021,11 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             }
             RT_CUDA(ctx, cudaEventRecord(s->ev_fork, st));
             RT_CUDA(ctx, cudaStreamWaitEvent(s->aux_stream, s->ev_fork, 0));
-            if (!base_ok) {
-                k_rng_init<<<div_up(div_up(npix, kRngRun), 128), 128, 0, s->aux_stream>>>(s->rng_base.p, npix, fp->seed,
-                                                              (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
-                s->launches += 1;
-                s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H; s->rng_off = fp->sample_offset;
-                s->rng_valid = true;
-                s->rng_lazy = false;
-            }
-            RT_CUDA(ctx, cudaMemcpyAsync(s->rng_cur.p, s->rng_base.p, 6 * (size_t)npix * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s->aux_stream));
+            k_rng_init<<<div_up(div_up(npix, kRngRun), 128), 128, 0, s->aux_stream>>>(s->rng_cur.p, s->rng_pix_off.p, fp->sample_offset, npix, fp->seed,
+                                                                                    (unsigned long long)fp->sample_offset * RT_RNG_SAMPLE_STRIDE);
+            s->launches += 1;
+            s->rng_seed = fp->seed; s->rng_w = W; s->rng_h = H;
+            s->rng_valid = true;
             RT_CUDA(ctx, cudaEventRecord(s->ev_join, s->aux_stream));
             rng_forked = true;
         }
@@ -1087,7 +1091,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, make_queue(s, 0, ref_mul), cnt + 2, s->result.p, s->ray_bins, fp->flags);
+            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done, make_queue(s, 0, ref_mul), cnt + 2, s->result.p, s->ray_bins, fp->flags);
             s->launches += 1;
             for (uint32_t d = 2; d <= D; d++) {
                 const Queue qin = make_queue(s, d & 1, ref_mul), qout = make_queue(s, (d + 1) & 1, ref_mul);
