@@ -367,6 +367,31 @@ __device__ __forceinline__ float qfloat(uint32_t w, uint32_t magic) {
     return __uint_as_float(r);
 }
 
+// Two bytes per PRMT (default; -DRT_BYTE_DEQ restores one byte per PRMT: 123.5 instead of 121.4 ms of traversal per C4
+// frame).  ncu (profiles/r5b_k_extend_wide_ncu.txt) shows the traversal kernel bound by the ALU pipe (70 % busy: PRMT,
+// FMNMX, LOP3, SEL, FSETP all live there) with the FMA pipe at 26 %.  Bytes j and j+1 of w, each with 0x64 above it, are
+// the two halves 1024 + q of one register (fp16 0x6400 | q = 1024 + q exactly); the two half -> float conversions
+// (HADD2.F32) run on the FMA pipe: 24 PRMT + 48 HADD2.F32 per node instead of 48 PRMT.  1024 is folded into the FMA
+// addend like 2^23 is for qfloat (and rounds that addend 2^13 times finer).  Moving more ALU work over was tried and is
+// slower: the hit mask from the sign bit of fma(thi, 1.000002, -tlo) via mul.hi / mad.lo (124.3 ms) and the near / far
+// word selects as integer multiply-adds (127.5 ms); both together 129.0 ms (r5d).
+template <int J>
+__device__ __forceinline__ void qfloat2(uint32_t w, uint32_t magic, float &f0, float &f1) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x5140 + J * 0x101));  // result bytes: w[J], magic[0], w[J+1], magic[1]
+    asm("{ .reg .b16 lo, hi; mov.b32 {lo, hi}, %2; cvt.f32.f16 %0, lo; cvt.f32.f16 %1, hi; }" : "=f"(f0), "=f"(f1) : "r"(r));
+}
+#ifndef RT_BYTE_DEQ
+#define RT_HALF_DEQ 1
+#endif
+#ifdef RT_HALF_DEQ
+#define RT_DEQ_MAGIC 0x64646464u
+#define RT_DEQ_BIAS 1024.0f
+#else
+#define RT_DEQ_MAGIC 0x4B000000u
+#define RT_DEQ_BIAS 8388608.0f
+#endif
+
 // Blackwell packed fp32: two fused multiply-adds per issue slot (FFMA2).  (d0, d1) = (a0, a1) * s + b
 // with s and b given as register pairs holding the same value twice.
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
@@ -465,7 +490,7 @@ __device__ __forceinline__ bool trav_tree_done(const WideTrav &t) { return !trav
 
 // One wide-node visit of a lane: pop the next node group entry, fetch the node (five 128-bit loads), slab-test
 // its 8 quantised child boxes, queue the hit internal children (octant order) and the hit leaf primitives.
-// `magic` must be 0x4B000000; it arrives as a kernel argument so that it lives in a register (qfloat).
+// `magic` must be RT_DEQ_MAGIC; it arrives as a kernel argument so that it lives in a register (qfloat / qfloat2).
 __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const float4 *__restrict__ wn, uint32_t magic,
                                           const uint8_t (*s_perm)[256]) {
     if ((t.gmask >> 8) == 0) {
@@ -486,9 +511,9 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
     const float sy = __uint_as_float(((eim >> 8) & 0xFFu) << 23) * t.iy;
     const float sz = __uint_as_float(((eim >> 16) & 0xFFu) << 23) * t.iz;
     // t = (2^23 + q) * s + (b - 2^23 * s), b = (origin - o) / d
-    const float bx = __fmaf_rn(-8388608.0f, sx, __fmaf_rn(w0.x, t.ix, t.ox));
-    const float by = __fmaf_rn(-8388608.0f, sy, __fmaf_rn(w0.y, t.iy, t.oy));
-    const float bz = __fmaf_rn(-8388608.0f, sz, __fmaf_rn(w0.z, t.iz, t.oz));
+    const float bx = __fmaf_rn(-RT_DEQ_BIAS, sx, __fmaf_rn(w0.x, t.ix, t.ox));
+    const float by = __fmaf_rn(-RT_DEQ_BIAS, sy, __fmaf_rn(w0.y, t.iy, t.oy));
+    const float bz = __fmaf_rn(-RT_DEQ_BIAS, sz, __fmaf_rn(w0.z, t.iz, t.oz));
     const unsigned long long sx2 = pack2(sx, sx), sy2 = pack2(sy, sy), sz2 = pack2(sz, sz);
     const unsigned long long bx2 = pack2(bx, bx), by2 = pack2(by, by), bz2 = pack2(bz, bz);
     const bool px = t.ix >= 0.0f, py = t.iy >= 0.0f, pz = t.iz >= 0.0f;
@@ -504,6 +529,26 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
 #pragma unroll
         for (int jp = 0; jp < 2; jp++) {
             float tnx[2], tfx[2], tny[2], tfy[2], tnz[2], tfz[2];
+#ifdef RT_HALF_DEQ
+            {
+                float a0, a1;
+                if (jp == 0) {
+                    qfloat2<0>(nx, magic, a0, a1); ffma2(tnx[0], tnx[1], a0, a1, sx2, bx2);
+                    qfloat2<0>(fx, magic, a0, a1); ffma2(tfx[0], tfx[1], a0, a1, sx2, bx2);
+                    qfloat2<0>(ny, magic, a0, a1); ffma2(tny[0], tny[1], a0, a1, sy2, by2);
+                    qfloat2<0>(fy, magic, a0, a1); ffma2(tfy[0], tfy[1], a0, a1, sy2, by2);
+                    qfloat2<0>(nz, magic, a0, a1); ffma2(tnz[0], tnz[1], a0, a1, sz2, bz2);
+                    qfloat2<0>(fz, magic, a0, a1); ffma2(tfz[0], tfz[1], a0, a1, sz2, bz2);
+                } else {
+                    qfloat2<2>(nx, magic, a0, a1); ffma2(tnx[0], tnx[1], a0, a1, sx2, bx2);
+                    qfloat2<2>(fx, magic, a0, a1); ffma2(tfx[0], tfx[1], a0, a1, sx2, bx2);
+                    qfloat2<2>(ny, magic, a0, a1); ffma2(tny[0], tny[1], a0, a1, sy2, by2);
+                    qfloat2<2>(fy, magic, a0, a1); ffma2(tfy[0], tfy[1], a0, a1, sy2, by2);
+                    qfloat2<2>(nz, magic, a0, a1); ffma2(tnz[0], tnz[1], a0, a1, sz2, bz2);
+                    qfloat2<2>(fz, magic, a0, a1); ffma2(tfz[0], tfz[1], a0, a1, sz2, bz2);
+                }
+            }
+#else
             if (jp == 0) {
                 ffma2(tnx[0], tnx[1], qfloat<0>(nx, magic), qfloat<1>(nx, magic), sx2, bx2);
                 ffma2(tfx[0], tfx[1], qfloat<0>(fx, magic), qfloat<1>(fx, magic), sx2, bx2);
@@ -519,6 +564,7 @@ __device__ __forceinline__ void trav_node(WideTrav &t, WideStack &stack, const f
                 ffma2(tnz[0], tnz[1], qfloat<2>(nz, magic), qfloat<3>(nz, magic), sz2, bz2);
                 ffma2(tfz[0], tfz[1], qfloat<2>(fz, magic), qfloat<3>(fz, magic), sz2, bz2);
             }
+#endif
 #pragma unroll
             for (int e = 0; e < 2; e++) {
                 const float tlo = fmaxf(fmaxf(tnx[e], tny[e]), fmaxf(tnz[e], t.tmin));

@@ -887,13 +887,13 @@ static int launch_extend(Scene *s, const SceneDev &sd, const ExtendIn &in, const
     RT_CUDA(ctx, prof_mark(s, st));
     if (s->wide) {
         if (s->extend_blocks_per_sm >= 8)
-            k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, RT_DEQ_MAGIC);
         else if (s->extend_blocks_per_sm == 7)
-            k_extend_wide<7><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<7><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, RT_DEQ_MAGIC);
         else if (s->extend_blocks_per_sm >= 6)
-            k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, RT_DEQ_MAGIC);
         else
-            k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, 0x4B000000u);
+            k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->t3, (int)s->fetch_min, RT_DEQ_MAGIC);
     }
     else
         k_extend<<<grid, 128, 0, st>>>(sd, in, n_ptr, n_fixed, fetch_ctr, hits, (int)s->t1, (int)s->t2, (int)s->fetch_min);
@@ -1070,13 +1070,13 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                 RT_CUDA(ctx, prof_mark(s, st));
                 const int t1 = (int)s->t1, t2 = (int)s->t2, t3 = (int)s->t3, fm = (int)s->fetch_min;
                 if (ref_mul)
-                    k_path<6, true><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                    k_path<6, true><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, RT_DEQ_MAGIC);
                 else if (s->extend_blocks_per_sm >= 8)
-                    k_path<8, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                    k_path<8, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, RT_DEQ_MAGIC);
                 else if (s->extend_blocks_per_sm == 7)
-                    k_path<7, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                    k_path<7, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, RT_DEQ_MAGIC);
                 else
-                    k_path<6, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, 0x4B000000u);
+                    k_path<6, false><<<grid, RT_EXTEND_THREADS, 0, st>>>(sd, pa, t1, t2, t3, fm, RT_DEQ_MAGIC);
                 RT_CUDA(ctx, prof_mark(s, st));
                 k_accumulate_hits<<<(uint32_t)ctx->sm_count * 8u, 256, 0, st>>>(s->result.p, s->hit_pix.p, n_hit, S, reinterpret_cast<float4 *>(out->accum_linear), fresh);
                 s->launches += 2;

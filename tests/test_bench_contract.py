@@ -66,3 +66,16 @@ def test_product_arm_fails_loudly_without_a_gpu():
     r = _run("--n-spheres", "1000", "--steps", "1", "--warmup", "0")
     assert r.returncode != 0
     assert "no CUDA device" in (r.stderr + r.stdout)
+
+
+def test_nested_step_functions_are_called_with_their_own_keywords():
+    """run_ours and run_c5 each define frame()/timed(); a call must only use keywords its own definition accepts
+    (a search-and-replace across both once broke the C5 arm, which no CPU test executes)."""
+    import ast
+    tree = ast.parse(open(os.path.join(ROOT, "bench.py")).read())
+    for fn in [n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name in ("run_ours", "run_c5")]:
+        defs = {n.name: [a.arg for a in n.args.args] for n in ast.walk(fn) if isinstance(n, ast.FunctionDef)}
+        for c in ast.walk(fn):
+            if isinstance(c, ast.Call) and isinstance(c.func, ast.Name) and c.func.id in defs:
+                for k in c.keywords:
+                    assert k.arg in defs[c.func.id], (fn.name, c.func.id, k.arg, c.lineno)
