@@ -698,7 +698,7 @@ def run_c5(a):
         for i in range(a.warmup):
             frame(i, e2e, prefetch=i + 1 < a.warmup)  # the first timed step copies its own inputs, inside the region
         barrier()
-        st0 = all_stats()
+        st0 = sc.stats()
         if sampler:
             sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -716,7 +716,7 @@ def run_c5(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(sg, op=dist.ReduceOp.SUM)
         return dict(ms=float(t.item()), segs=float(sg.item()), trace_ms=float(st1.trace_ms), build_ms=float(st1.build_ms),
-                    launches=int(st1["kernel_launches"] - st0["kernel_launches"]), st=st1)
+                    launches=int(st1.kernel_launches - st0.kernel_launches), st=st1)
 
     sampler = ClockSampler(local) if rank == 0 else None
     dv = timed(False, sampler)
@@ -734,7 +734,7 @@ def run_c5(a):
         bseg = seg_bytes(n_prims)
         seg_step = dv["segs"] / world_size / a.steps
         trace_step = dv["trace_ms"] / a.steps
-        n_launch = max(1, int(st["trace_launches"]))
+        n_launch = max(1, int(st.trace_launches))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
         line = {
             "metric": "Mrays/s", "value": dv["segs"] / (dv["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
