@@ -214,7 +214,12 @@ int rt_transforms_time(rt_context ctx, const float *dev_positions, const float *
                        const float particle_scale[3], float *dev_transforms_out, void *stream);
 
 /* ---- launch: replaces optixLaunch(pipeline, stream, params, sbt, w, h, 1) and the raygen /
- *      closest-hit / miss programs of shader/Shader.cu ---------------------------------------- */
+ *      closest-hit / miss programs of shader/Shader.cu.  Stream-ordered.  One host-side wait by default: the ray
+ *      queues of the wavefront form are sized from the frame's own primary-hit count, which rt_render reads back (4 bytes)
+ *      after the primary-visibility pass it has enqueued, i.e. the call returns once `stream` has reached that point
+ *      (build + primary pass; the reference synchronises the whole device after every launch, RendererTime.cu:500).
+ *      rt_scene_set_option(scene, "compact_queues", 0) sizes the queues for every pixel instead (3x the device memory
+ *      on BASELINE config 4) and never blocks; option "fused" uses no queues at all. ----------------------------- */
 int rt_render(rt_scene scene, const rt_camera *camera, const rt_frame_params *params,
               const rt_outputs *out, void *stream);
 

@@ -121,6 +121,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     else if (k == "batch_spp") s.batch_spp = (uint32_t)std::min<int64_t>(64, std::max<int64_t>(0, value));
     else if (k == "wide") { s.wide = value != 0; s.built = false; }
     else if (k == "fused") s.fused = value != 0;
+    else if (k == "compact_queues") s.compact_queues = value != 0;
     else if (k == "chunk_spp") s.chunk_spp = (uint32_t)std::min<int64_t>(1024, std::max<int64_t>(1, value));
     else if (k == "compat_shading") { s.compat = (uint32_t)(value & 3); s.built = false; }
     else if (k == "t1") s.t1 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));

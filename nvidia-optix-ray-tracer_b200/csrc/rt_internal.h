@@ -209,6 +209,7 @@ struct Scene {
     DevBuf<uint32_t> hit_pix;     // fused form: pixels whose primary ray hit something
     DevBuf<uint32_t> rng_start;   // fused form: [sample][6][npix] XORWOW state of stream(p, s) per hit pixel
     DevBuf<uint32_t> rng_pix_off; // sample offset the state of pixel p in rng_cur stands at (lazy stepping: only pixels that hit draw)
+    bool compact_queues = true;   // option "compact_queues": size the wavefront queues from the frame's primary-hit count (one stream sync per rt_render)
     bool fused = false;           // option "fused": one persistent path kernel instead of per-bounce wavefront launches
     uint32_t chunk_spp = 16;      // option "chunk_spp": samples per work unit of the fused kernel
     DevBuf<float4> hit;           // per queue entry: t, bits(slot), u, v (written by k_extend)

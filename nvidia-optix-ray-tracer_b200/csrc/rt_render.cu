@@ -851,6 +851,22 @@ __global__ void k_import_hits(const float4 *__restrict__ ext, const uint32_t *__
     phit[i] = h;
 }
 
+// pixels whose primary ray hit something: what the wavefront queues of this frame have to hold per sample in flight
+__global__ void __launch_bounds__(1024)
+k_count_hits(const float4 *__restrict__ phit, uint32_t npix, uint32_t *__restrict__ out) {
+    __shared__ uint32_t s_w[32];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool hit = i < npix && __float_as_uint(phit[i].y) != kNoSlot;
+    const uint32_t c = __popc(__ballot_sync(0xFFFFFFFFu, hit));
+    if ((threadIdx.x & 31u) == 0) s_w[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        uint32_t v = s_w[threadIdx.x];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        if (threadIdx.x == 0 && v) atomicAdd(out, v);
+    }
+}
+
 // cumulative segment counter (device side, so that no host read is needed between frames)
 __global__ void k_tally(const uint32_t *__restrict__ counters, uint32_t n_cnt, uint32_t primary, unsigned long long *total) {
     if (threadIdx.x || blockIdx.x) return;
@@ -952,9 +968,17 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     const uint32_t D = fp->max_depth;
 
     RT_CUDA(ctx, s->phit.reserve(npix, &s->bytes));
-    const size_t qn = fused ? (size_t)npix : std::max((size_t)npix, spp ? (size_t)npix * std::min(Sb, spp) : (size_t)0);
+    // Wavefront queues hold one entry per (continuing pixel, sample in flight).  With option "compact_queues" (default) they
+    // are sized from THIS frame's primary-hit count, read back after the primary-visibility pass (one 4-byte copy and a
+    // stream synchronisation per rt_render: the host waits for the build + primary pass it has just enqueued, ~4 ms on C4,
+    // and then enqueues the bounces; nothing is idle but the few microseconds of launch latency).  Without it they are
+    // sized for every pixel (C4: 44.6 GB instead of 9.7 GB) and rt_render never blocks.
+    const bool compact = spp && !fused && s->compact_queues;
+    const size_t qn_full = std::max((size_t)npix, spp ? (size_t)npix * std::min(Sb, spp) : (size_t)0);
+    const size_t qn = (fused || compact) ? (size_t)npix : qn_full;
+    const size_t rn = fused ? (size_t)npix : qn_full;  // result: one entry per (pixel, sample in flight)
     for (int k = 0; k < 2; k++) {
-        const size_t qk = (k == 0 || (spp && !fused)) ? qn : 1;  // primary rays use queue 0's origin/direction arrays
+        const size_t qk = (k == 0 || (spp && !fused && !compact)) ? qn : 1;  // primary rays use queue 0's origin/direction arrays
         RT_CUDA(ctx, s->q_o[k].reserve(qk, &s->bytes));
         RT_CUDA(ctx, s->q_d[k].reserve(qk, &s->bytes));
     }
@@ -967,14 +991,18 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     } else if (spp) {
         RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
         RT_CUDA(ctx, s->rng_pix_off.reserve(npix, &s->bytes));
-        for (int k = 0; k < 2; k++) {
-            RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
-            RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
-            RT_CUDA(ctx, s->q_r4[k].reserve(qn, &s->bytes));
-            if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qn, &s->bytes));
+        if (!compact) {
+            for (int k = 0; k < 2; k++) {
+                RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
+                RT_CUDA(ctx, s->q_r[k].reserve(qn, &s->bytes));
+                RT_CUDA(ctx, s->q_r4[k].reserve(qn, &s->bytes));
+                if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qn, &s->bytes));
+            }
+            RT_CUDA(ctx, s->hit.reserve(qn, &s->bytes));
+        } else {
+            RT_CUDA(ctx, s->prim_fetch.reserve(1, &s->bytes));
         }
-        RT_CUDA(ctx, s->hit.reserve(qn, &s->bytes));
-        RT_CUDA(ctx, s->result.reserve(qn, &s->bytes));
+        RT_CUDA(ctx, s->result.reserve(rn, &s->bytes));
     }
     // counters: [n_batches][D+3] queue sizes, then one fetch counter per k_extend launch
     // fused: [n_batches] segment counters (summed by k_tally / rt_get_stats like the queue sizes), then [n_batches]
@@ -1051,6 +1079,27 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         s->launches += 1;
     }
 
+    if (compact) {
+        uint32_t n_hit = 0;
+        if (D > 1) {
+            RT_CUDA(ctx, cudaMemsetAsync(s->prim_fetch.p, 0, sizeof(uint32_t), st));
+            k_count_hits<<<div_up(npix, 1024), 1024, 0, st>>>(phit, npix, s->prim_fetch.p);
+            s->launches += 1;
+            RT_CUDA(ctx, cudaMemcpyAsync(&n_hit, s->prim_fetch.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            RT_CUDA(ctx, cudaStreamSynchronize(st));
+        }
+        const size_t need = (size_t)std::max(n_hit, 1u) * std::min(Sb, spp);
+        const size_t qc = need + need / 8;  // head room: the hit count moves a little from frame to frame (buffers only grow)
+        for (int k = 0; k < 2; k++) {
+            RT_CUDA(ctx, s->q_o[k].reserve(k == 0 ? std::max(qc, (size_t)npix) : qc, &s->bytes));
+            RT_CUDA(ctx, s->q_d[k].reserve(k == 0 ? std::max(qc, (size_t)npix) : qc, &s->bytes));
+            RT_CUDA(ctx, s->q_t[k].reserve(qc, &s->bytes));
+            RT_CUDA(ctx, s->q_r[k].reserve(qc, &s->bytes));
+            RT_CUDA(ctx, s->q_r4[k].reserve(qc, &s->bytes));
+            if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qc, &s->bytes));
+        }
+        RT_CUDA(ctx, s->hit.reserve(qc, &s->bytes));
+    }
     if (spp && fused) {
         if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
         const uint32_t grid = (uint32_t)ctx->sm_count * s->extend_blocks_per_sm;

@@ -93,12 +93,22 @@ def test_fused_reproduces_reference_shader_golden(pkg, synth, idx):
 def test_fused_uses_a_fraction_of_the_wavefront_memory(pkg, synth):
     d = scenes.random_scene(pkg, synth, 20000, seed=2)
     cam = pkg.camera_configure([2.2, 0.2, 0.3], [0, 0, 0], [0, 0, 1], False)
-    a = scenes.GpuScene(pkg, d)
+    a = scenes.GpuScene(pkg, d, options={"compact_queues": 0})   # queues sized for every pixel, rt_render never blocks
     b = scenes.GpuScene(pkg, d, options={"fused": 1})
+    c = scenes.GpuScene(pkg, d)                                   # default: queues sized from the frame's primary-hit count
     ra = a.render(cam, 640, 360, 16, 5, 3, want=("accum",))
     rb = b.render(cam, 640, 360, 16, 5, 3, want=("accum",))
-    assert np.array_equal(bits(ra["accum"]), bits(rb["accum"]))
+    rc = c.render(cam, 640, 360, 16, 5, 3, want=("accum",))
+    assert np.array_equal(bits(ra["accum"]), bits(rb["accum"])) and np.array_equal(bits(ra["accum"]), bits(rc["accum"]))
+    assert ra["segments"] == rb["segments"] == rc["segments"]
     assert rb["stats"].device_bytes < 0.4 * ra["stats"].device_bytes
+    assert rc["stats"].device_bytes < ra["stats"].device_bytes
     assert rb["stats"].kernel_launches < ra["stats"].kernel_launches
+    # a frame with MORE hit pixels than the one the compact queues were sized for: they grow, same result as the full ones
+    cam2 = pkg.camera_configure([1.2, 0.1, 0.2], [0, 0, 0], [0, 0, 1], False)
+    ra2 = a.render(cam2, 640, 360, 16, 5, 3, want=("accum",))
+    rc2 = c.render(cam2, 640, 360, 16, 5, 3, want=("accum",))
+    assert np.array_equal(bits(ra2["accum"]), bits(rc2["accum"])) and ra2["segments"] == rc2["segments"]
     a.close()
     b.close()
+    c.close()
