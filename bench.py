@@ -626,6 +626,59 @@ def run_ours(a):
 
 
 # ---------------------------------------------------------------------------------------------------
+def c5_parity(a, pkg, synth, torch, ctx, sc, d_base_c, d_base_r, d_vel, d_c, d_r, n, dt, frames_total, stream, n_rays=32):
+    """Parity at the C5 size: the closest hits of sampled camera rays and of rays scattered from those hits, traced through
+    the rebuilt 8-wide tree of one frame (rt_trace_rays), against the CPU oracle's BRUTE FORCE over all ~10^8 spheres of
+    that frame: primitive ids and t bit for bit.  The oracle is the checker here, never the thing measured."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    orc = oracle_lib.load()
+    f = 3
+    ctx.spheres_advect(d_base_c.data_ptr(), d_base_r.data_ptr(), d_vel.data_ptr(), n, dt * frames_total, frames_total, f,
+                       [0.0, 0.0, 0.0], [1.0, 1.0, 1.0], d_c.data_ptr(), d_r.data_ptr(), stream)
+    sc.build(stream)
+    torch.cuda.synchronize()
+    spheres = np.concatenate([d_c.cpu().numpy().reshape(n, 3), d_r.cpu().numpy().reshape(n, 1)], 1).astype(np.float32)
+    world = dict(kind_index=np.arange(n, dtype=np.uint32), mat=np.arange(n, dtype=np.uint32), spheres=spheres,
+                 tri_verts=np.zeros((0, 9), np.float32), tri_normals=np.zeros((0, 9), np.float32),
+                 roughs=np.float32([[0.5, 0.5, 0.5]]), metals=np.float32([[0.8, 0.85, 0.88, 0.0]]))
+    cam = pkg.camera_configure(**synth.c5_camera(f, dt))
+    rng = np.random.default_rng(11)
+    W, H = a.width, a.height
+    px = rng.integers(int(0.25 * H), int(0.75 * H), n_rays) * W + rng.integers(int(0.36 * W), int(0.64 * W), n_rays)
+    x, y = (px % W).astype(np.float32), (px // W).astype(np.float32)
+    nx = ((x + np.float32(0.5)) / np.float32(W)) * np.float32(2) - np.float32(1)
+    ny = ((y + np.float32(0.5)) / np.float32(H)) * np.float32(2) - np.float32(1)
+    U, V, Wv, C0 = (np.float32(list(v)) for v in (cam.U, cam.V, cam.W, cam.center))
+    d = ((nx * (np.float32(W) / np.float32(H)))[:, None] * U + ny[:, None] * V + Wv).astype(np.float32)
+    rays = np.concatenate([np.broadcast_to(C0, d.shape), np.full((n_rays, 1), 1e-6, np.float32), d, np.full((n_rays, 1), 1e16, np.float32)], 1).astype(np.float32)
+
+    def gpu_trace(r, skip=None):
+        dr = torch.from_numpy(np.ascontiguousarray(r)).cuda()
+        ds = torch.from_numpy(np.ascontiguousarray(skip, np.uint32).view(np.int32)).cuda() if skip is not None else None
+        t = torch.empty(len(r), dtype=torch.float32, device="cuda")
+        i = torch.empty(len(r), dtype=torch.int32, device="cuda")
+        sc.trace_rays(dr.data_ptr(), ds.data_ptr() if ds is not None else None, len(r), t.data_ptr(), i.data_ptr(), stream)
+        torch.cuda.synchronize()
+        return t.cpu().numpy(), i.cpu().numpy().view(np.uint32)
+
+    t0 = time.time()
+    ot, oi = orc.trace(world, rays, accel=0)
+    gt, gi = gpu_trace(rays)
+    hit = oi != 0xFFFFFFFF
+    bad = int((oi != gi).sum() + (ot.view(np.uint32) != gt.view(np.uint32)).sum())
+    o2 = (rays[hit, 0:3] + ot[hit, None] * rays[hit, 4:7]).astype(np.float32)
+    d2 = rng.normal(size=o2.shape).astype(np.float32)
+    rays2 = np.concatenate([o2, np.full((len(o2), 1), 1e-6, np.float32), d2, np.full((len(o2), 1), 1e16, np.float32)], 1).astype(np.float32)
+    ot2, oi2 = orc.trace(world, rays2, skip=oi[hit], accel=0)
+    gt2, gi2 = gpu_trace(rays2, oi[hit])
+    bad2 = int((oi2 != gi2).sum() + (ot2.view(np.uint32) != gt2.view(np.uint32)).sum())
+    return {"against": "CPU oracle brute force over every sphere of frame %d" % f, "n_prims": int(n), "primary_rays": int(n_rays),
+            "primary_hits": int(hit.sum()), "primary_mismatch": bad, "scattered_rays": int(len(rays2)),
+            "scattered_hits": int((oi2 != 0xFFFFFFFF).sum()), "scattered_mismatch": bad2, "oracle_seconds": round(time.time() - t0, 1)}
+
+
+# ---------------------------------------------------------------------------------------------------
 def run_c5(a):
     """BASELINE config 5: DEM packing time series, frame-parallel.  One step = every rank takes the next
     frame of the series (frame = step * world + rank): device-side particle update (rt_spheres_advect, the
@@ -767,6 +820,8 @@ def run_c5(a):
             "segments_per_step": seg_step,
             "cpu_baseline": None,
         }
+        if not a.no_cpu_baseline:
+            line["parity_check"] = c5_parity(a, pkg, synth, torch, ctx, sc, d_base_c, d_base_r, d_vel, d_c, d_r, n, dt, frames_total, stream)
         print(json.dumps(line))
     if world_size > 1:
         dist.barrier()
