@@ -129,7 +129,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     else if (k == "t3") s.t3 = (uint32_t)std::min<int64_t>(33, std::max<int64_t>(0, value));
     else if (k == "fetch_min") s.fetch_min = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));
     else if (k == "ray_bins") s.ray_bins = value >= 24 ? 24u : 8u;
-    else if (k == "shade_threads") s.shade_threads = value >= 1024 ? 1024u : 512u;
+    else if (k == "shade_threads") s.shade_threads = value >= 1024 ? 1024u : (value <= 256 ? 256u : 512u);
     else if (k == "collapse_mode") { s.collapse_mode = (uint32_t)std::min<int64_t>(1, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "refit_mode") { s.refit_mode = (uint32_t)std::min<int64_t>(2, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "extend_blocks_per_sm") s.extend_blocks_per_sm = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));

@@ -218,7 +218,7 @@ struct Scene {
     DevBuf<uint32_t> u_skip;      // rt_trace_rays: skip slot per ray (+1 fetch counter)
     uint32_t t1 = 16, t2 = 4, t3 = 0, fetch_min = 4;  // traversal thresholds (see extend_warp / extend_warp_wide)
     uint32_t extend_blocks_per_sm = 7;
-    uint32_t ray_bins = 8, shade_threads = 512;  // queue grouping of scattered rays (rt_render.cu binned_push)
+    uint32_t ray_bins = 8, shade_threads = 256;  // queue grouping of scattered rays (rt_render.cu binned_push)
     uint32_t collapse_mode = 0;   // 0: k_collapse (one thread per wide node); 1: k_collapse8 (eight lanes per wide node)
     uint32_t refit_mode = 1;      // 0: one kernel, global counters; 1: k_refit_local (shared-memory climb) + k_refit_top; 2: k_refit_rmq (range queries) + k_refit_top
     DevBuf<uint32_t> counters;    // queue counters

@@ -392,7 +392,7 @@ k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uin
 // One thread per queue entry: reads the ray, its hit record (written by k_extend) and the path's RNG
 // state, applies Shader.cu:94-242 / :276-287 and appends the scattered ray to the next queue.
 template <int kShadeThreads, bool kRefMul>
-__global__ void __launch_bounds__(kShadeThreads, kShadeThreads == 512 ? 3 : 1)
+__global__ void __launch_bounds__(kShadeThreads, kShadeThreads == 512 ? 3 : (kShadeThreads == 256 ? 6 : 1))
 k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const float4 *__restrict__ hits, Queue out,
         uint32_t *out_count, float4 *__restrict__ result, uint32_t depth, uint32_t max_depth, F3 bg, uint32_t nb, uint32_t flags) {
     __shared__ uint32_t s_cnt[kShadeThreads / 32][kBins + 1];
@@ -1149,6 +1149,8 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                 if (rc) return rc;
                 if (ref_mul)
                     k_shade<512, true><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
+                else if (s->shade_threads <= 256)  // small blocks (40 registers): one fits next to six resident traversal blocks
+                    k_shade<256, false><<<(uint32_t)ctx->sm_count * 6u, 256, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
                 else if (s->shade_threads >= 1024)
                     k_shade<1024, false><<<(uint32_t)ctx->sm_count * 2u, 1024, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
                 else
