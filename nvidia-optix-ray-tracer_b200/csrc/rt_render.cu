@@ -1,7 +1,7 @@
 // rt_render.cu — wavefront path tracer kernels for sm_100a.
 //
 // Replaces the OptiX programs of the reference:
-//   __raygen__raygenProgram            shader/Shader.cu:246-273   -> k_primary / k_shade_primary
+//   __raygen__raygenProgram            shader/Shader.cu:246-273   -> k_raygen / k_prepare / k_shade_first
 //   closesthitImpl (4 closest-hit PGs) shader/Shader.cu:94-242    -> scatter()
 //   __miss__missProgram                shader/Shader.cu:276-287   -> miss branches
 //   __initializeDeviceRandomGenerators src/Global/HostFunctions.cu:122-136 -> k_rng_init
@@ -311,80 +311,60 @@ k_primary_aov(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, const float4 *__r
     }
 }
 
-// ------------------------------------------------------------------ first bounce for S samples of every pixel
-// The reference has no sub-pixel jitter (Shader.cu:249-252), so all samples of a pixel share the
-// primary hit; each sample continues with its own XORWOW stream(p, s).
-constexpr int kPrimaryThreads = 512;
-__global__ void __launch_bounds__(kPrimaryThreads)
-k_shade_primary(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg,
-                const float4 *__restrict__ phit, uint32_t *__restrict__ rng, uint32_t *__restrict__ rng_off, unsigned long long seed,
-                uint32_t sample_offset, Queue out, uint32_t *out_count, float4 *__restrict__ result, uint32_t nb, uint32_t flags) {
-    __shared__ uint32_t s_cnt[kPrimaryThreads / 32][kBins + 1];
+// ------------------------------------------------------------------ first bounce: one thread per (hit pixel, sample)
+// The reference has no sub-pixel jitter (Shader.cu:249-252), so all samples of a pixel share the primary hit; each
+// sample continues with its own XORWOW stream(p, s).  k_prepare has compacted the pixels that continue a path
+// (hit_pix / n_hit), settled the others in the accumulation buffer and stored the stream state at the start of every
+// sample (rng_start), so the samples are independent here: every lane has work (the per-pixel loop this replaces kept
+// 76 % of C4's lanes idle through 32 block-wide queue appends and wrote 3.2 GB of background colour per batch).
+// Path id = i * S + s: result[] holds hit pixels only and is summed in sample order by k_accumulate_hits.
+constexpr int kFirstThreads = 512;
+__global__ void __launch_bounds__(kFirstThreads)
+k_shade_first(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, const float4 *__restrict__ phit,
+              const uint32_t *__restrict__ hit_pix, const uint32_t *__restrict__ n_hit, const uint32_t *__restrict__ rng_start,
+              uint32_t cap, Queue out, uint32_t *out_count, uint32_t nb, uint32_t flags) {
+    __shared__ uint32_t s_cnt[kFirstThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
-    uint32_t x, y;
-    const bool valid = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, W, H, x, y);
-    const uint32_t npix = W * H;
-    const uint32_t p = valid ? y * W + x : 0u;
-    Ray ray;
-    Hit hit;
-    Rng st = {0, 0, 0, 0, 0, 0};
-    hit.slot = kNoSlot;
-    if (valid) {
-        ray = primary_ray(cam, x, y, W, H);
-        const float4 h = phit[p];
-        hit.t = h.x;
-        hit.slot = __float_as_uint(h.y);
-        hit.u = h.z;
-        hit.v = h.w;
-    }
-    const bool is_hit = valid && hit.slot != kNoSlot;
-    const bool go = is_hit && max_depth > 1u;  // Shader.cu:102-107 with depth == 1
-    // Only pixels that continue a path draw random numbers, so only their streams are touched: a pixel's state is
-    // advanced lazily, from the sample it stands at (rng_off) to this launch's first sample, when the pixel needs it
-    // (C4: 76 % of the pixels miss; stepping every pixel's stream by S * 32 draws was a third of this kernel).
-    if (go) {
-        const uint32_t have = rng_off[p];
-        if (have > sample_offset || sample_offset - have > kRngMaxLag) {
-            curandStateXORWOW cs;
-            curand_init(seed, (unsigned long long)p, (unsigned long long)sample_offset * RT_RNG_SAMPLE_STRIDE, &cs);
-            st.d = cs.d; st.v0 = cs.v[0]; st.v1 = cs.v[1]; st.v2 = cs.v[2]; st.v3 = cs.v[3]; st.v4 = cs.v[4];
-        } else {
-            st.d = rng[0 * (size_t)npix + p];
-            st.v0 = rng[1 * (size_t)npix + p];
-            st.v1 = rng[2 * (size_t)npix + p];
-            st.v2 = rng[3 * (size_t)npix + p];
-            st.v3 = rng[4 * (size_t)npix + p];
-            st.v4 = rng[5 * (size_t)npix + p];
-            for (uint32_t k = (sample_offset - have) * RT_RNG_SAMPLE_STRIDE; k > 0; k--) (void)rng_next(st);
-        }
-    }
-    for (uint32_t s = 0; s < S; s++) {
-        const size_t pid = (size_t)p * S + s;
+    const uint32_t n = *n_hit;
+    // a block pass = 16 consecutive hit pixels x 32 samples (at S >= 32): the 16 lanes of a half warp read 64 contiguous bytes of
+    // every rng_start word, and all samples of a pixel enter the queue together, next to their neighbours' (rays that
+    // start from the same hit point walk the same nodes: queueing sample-major over the whole frame cost 2.5 % of
+    // the traversal time)
+    // (fewer samples per launch: SP = the power of two >= min(S, 32) sample slots, 512 / SP pixels per pass)
+    uint32_t sp_log = 0;
+    while ((1u << sp_log) < S && sp_log < 5u) sp_log++;
+    const uint32_t pi_log = 9u - sp_log;  // kFirstThreads = 512
+    const uint32_t il = threadIdx.x & ((1u << pi_log) - 1u), sl = threadIdx.x >> pi_log;
+    const uint32_t n_groups = (n + (1u << pi_log) - 1u) >> pi_log, s_passes = (S + (1u << sp_log) - 1u) >> sp_log;
+    for (uint32_t w = blockIdx.x; w < n_groups * s_passes; w += gridDim.x) {  // block-uniform trip count
+        const uint32_t g = w / s_passes, smp = ((w - g * s_passes) << sp_log) + sl, i = (g << pi_log) + il;
+        const bool valid = i < n && smp < S;
         Scatter sc1;
-        Rng r = st;
-        if (go) sc1 = scatter(sc, ray, hit, r);
-        const uint32_t qi = binned_push<kPrimaryThreads / 32>(out_count, go, go ? dir_bin(sc1.dir, nb) : 0u, nb, s_cnt, s_base);
-        if (go) {
+        Rng r = {0, 0, 0, 0, 0, 0};
+        uint32_t pid = 0, slot = kNoSlot;
+        if (valid) {
+            const uint32_t p = hit_pix[i];
+            const Ray ray = primary_ray(cam, p % W, p / W, W, H);
+            const float4 h = phit[p];
+            Hit hit;
+            hit.t = h.x;
+            hit.slot = __float_as_uint(h.y);
+            hit.u = h.z;
+            hit.v = h.w;
+            const uint32_t *rs = rng_start + (size_t)smp * 6u * cap + i;
+            r.d = rs[0];
+            r.v0 = rs[1 * (size_t)cap]; r.v1 = rs[2 * (size_t)cap]; r.v2 = rs[3 * (size_t)cap];
+            r.v3 = rs[4 * (size_t)cap]; r.v4 = rs[5 * (size_t)cap];
+            sc1 = scatter(sc, ray, hit, r);
+            pid = i * S + smp;
             // Shader.cu:230-233: the reference relies on tmin alone; by default the ray skips the primitive it leaves
-            queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, (uint32_t)pid, (flags & RT_FLAG_REF_NO_SELF_SKIP) ? kNoSlot : hit.slot, r);
+            slot = (flags & RT_FLAG_REF_NO_SELF_SKIP) ? kNoSlot : hit.slot;
+        }
+        const uint32_t qi = binned_push<kFirstThreads / 32>(out_count, valid, valid ? dir_bin(sc1.dir, nb) : 0u, nb, s_cnt, s_base);
+        if (valid) {
+            queue_write(out, qi, sc1.P, sc1.dir, sc1.alb, pid, slot, r);
             if (out.m) out.m[qi] = make_uint4(sc1.mat, 0u, 0u, 0u);
-        } else if (valid) {
-            // miss: 1 * background (Shader.cu:276-287); depth cut-off: 0 (:102-107)
-            result[pid] = is_hit ? make_float4(0, 0, 0, 0) : make_float4(1.0f * bg.x, 1.0f * bg.y, 1.0f * bg.z, 0.0f);
         }
-        if (go) {
-#pragma unroll 8
-            for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
-        }
-    }
-    if (go) {
-        rng_off[p] = sample_offset + S;
-        rng[0 * (size_t)npix + p] = st.d;
-        rng[1 * (size_t)npix + p] = st.v0;
-        rng[2 * (size_t)npix + p] = st.v1;
-        rng[3 * (size_t)npix + p] = st.v2;
-        rng[4 * (size_t)npix + p] = st.v3;
-        rng[5 * (size_t)npix + p] = st.v4;
     }
 }
 
@@ -672,7 +652,7 @@ constexpr int kPrepThreads = 256;
 __global__ void __launch_bounds__(kPrepThreads)
 k_prepare(uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg, const float4 *__restrict__ phit, uint32_t *__restrict__ rng,
           uint32_t *__restrict__ rng_off, unsigned long long seed, uint32_t sample_offset, uint32_t *__restrict__ hit_pix,
-          uint32_t *__restrict__ n_hit, uint32_t *__restrict__ rng_start, float4 *__restrict__ accum, int fresh) {
+          uint32_t *__restrict__ n_hit, uint32_t *__restrict__ rng_start, uint32_t cap, float4 *__restrict__ accum, int fresh) {
     __shared__ uint32_t s_warp[kPrepThreads / 32];
     __shared__ uint32_t s_base;
     uint32_t x, y;
@@ -728,13 +708,13 @@ k_prepare(uint32_t W, uint32_t H, uint32_t S, uint32_t max_depth, F3 bg, const f
         for (uint32_t k = (sample_offset - have) * RT_RNG_SAMPLE_STRIDE; k > 0; k--) (void)rng_next(st);
     }
     for (uint32_t s = 0; s < S; s++) {
-        uint32_t *rs = rng_start + (size_t)s * 6u * npix + i;
+        uint32_t *rs = rng_start + (size_t)s * 6u * cap + i;  // [sample][word][hit pixel], stride cap >= number of hit pixels
         rs[0] = st.d;
-        rs[1 * (size_t)npix] = st.v0;
-        rs[2 * (size_t)npix] = st.v1;
-        rs[3 * (size_t)npix] = st.v2;
-        rs[4 * (size_t)npix] = st.v3;
-        rs[5 * (size_t)npix] = st.v4;
+        rs[1 * (size_t)cap] = st.v0;
+        rs[2 * (size_t)cap] = st.v1;
+        rs[3 * (size_t)cap] = st.v2;
+        rs[4 * (size_t)cap] = st.v3;
+        rs[5 * (size_t)cap] = st.v4;
 #pragma unroll 8
         for (uint32_t k = 0; k < RT_RNG_SAMPLE_STRIDE; k++) (void)rng_next(st);
     }
@@ -764,22 +744,6 @@ k_accumulate_hits(const float4 *__restrict__ result, const uint32_t *__restrict_
         a.w += (float)S;
         accum[p] = a;
     }
-}
-
-// ------------------------------------------------------------------ ordered accumulation of a sample batch
-__global__ void __launch_bounds__(256)
-k_accumulate(const float4 *__restrict__ result, uint32_t S, uint32_t npix, float4 *__restrict__ accum, int fresh) {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    float4 a = fresh ? make_float4(0, 0, 0, 0) : accum[p];
-    for (uint32_t s = 0; s < S; s++) {
-        const float4 r = result[(size_t)p * S + s];
-        a.x += r.x;
-        a.y += r.y;
-        a.z += r.z;
-    }
-    a.w += (float)S;
-    accum[p] = a;
 }
 
 // ------------------------------------------------------------------ resolve: mean, clamp, sRGB, quantise
@@ -991,6 +955,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     } else if (spp) {
         RT_CUDA(ctx, s->rng_cur.reserve(6 * (size_t)npix, &s->bytes));
         RT_CUDA(ctx, s->rng_pix_off.reserve(npix, &s->bytes));
+        RT_CUDA(ctx, s->hit_pix.reserve(npix, &s->bytes));
         if (!compact) {
             for (int k = 0; k < 2; k++) {
                 RT_CUDA(ctx, s->q_t[k].reserve(qn, &s->bytes));
@@ -999,16 +964,18 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                 if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qn, &s->bytes));
             }
             RT_CUDA(ctx, s->hit.reserve(qn, &s->bytes));
+            RT_CUDA(ctx, s->result.reserve(rn, &s->bytes));
+            RT_CUDA(ctx, s->rng_start.reserve((size_t)std::min(Sb, spp) * 6 * npix, &s->bytes));
         } else {
             RT_CUDA(ctx, s->prim_fetch.reserve(1, &s->bytes));
         }
-        RT_CUDA(ctx, s->result.reserve(rn, &s->bytes));
     }
     // counters: [n_batches][D+3] queue sizes, then one fetch counter per k_extend launch
     // fused: [n_batches] segment counters (summed by k_tally / rt_get_stats like the queue sizes), then [n_batches]
     // hit-pixel counts, [n_batches] unit counters and the primary pass's fetch counter
     const size_t n_cnt = fused ? (size_t)(n_batches ? n_batches : 1) : (size_t)(n_batches ? n_batches : 1) * (D + 3);
-    const size_t n_fetch = fused ? 1 + 2 * (size_t)n_batches : 1 + (size_t)n_batches * (D + 1);
+    // (wavefront: then one hit-pixel count per batch)
+    const size_t n_fetch = fused ? 1 + 2 * (size_t)n_batches : 1 + (size_t)n_batches * (D + 1) + n_batches;
     RT_CUDA(ctx, s->counters.reserve(n_cnt + n_fetch, &s->bytes));
     if (!s->seg_total.p) {
         RT_CUDA(ctx, s->seg_total.reserve(1, &s->bytes));
@@ -1079,6 +1046,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         s->launches += 1;
     }
 
+    uint32_t hit_cap = npix;  // stride of rng_start = capacity in hit pixels
     if (compact) {
         uint32_t n_hit = 0;
         if (D > 1) {
@@ -1099,6 +1067,9 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             if (ref_mul) RT_CUDA(ctx, s->q_m[k].reserve(qc, &s->bytes));
         }
         RT_CUDA(ctx, s->hit.reserve(qc, &s->bytes));
+        RT_CUDA(ctx, s->result.reserve(qc, &s->bytes));
+        RT_CUDA(ctx, s->rng_start.reserve(6 * qc, &s->bytes));
+        hit_cap = (uint32_t)std::min<size_t>(qc / std::min(Sb, spp), npix);  // hit pixels the buffers can hold
     }
     if (spp && fused) {
         if (rng_forked) RT_CUDA(ctx, cudaStreamWaitEvent(st, s->ev_join, 0));
@@ -1109,7 +1080,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
             uint32_t *seg_ctr = s->counters.p + b, *n_hit = s->counters.p + n_cnt + b, *unit_ctr = s->counters.p + n_cnt + n_batches + b;
             k_prepare<<<div_up(tiles * 32u, kPrepThreads), kPrepThreads, 0, st>>>(W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done,
-                                                                                  s->hit_pix.p, n_hit, s->rng_start.p, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+                                                                                  s->hit_pix.p, n_hit, s->rng_start.p, npix, reinterpret_cast<float4 *>(out->accum_linear), fresh);
             s->launches += 1;
             if (D > 1) {
                 PathArgs pa;
@@ -1140,8 +1111,14 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         for (uint32_t b = 0; b < n_batches; b++) {
             const uint32_t S = std::min(Sb, spp - done);
             uint32_t *cnt = s->counters.p + (size_t)b * (D + 3);
-            k_shade_primary<<<div_up(tiles * 32u, kPrimaryThreads), kPrimaryThreads, 0, st>>>(sd, cd, W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done, make_queue(s, 0, ref_mul), cnt + 2, s->result.p, s->ray_bins, fp->flags);
-            s->launches += 1;
+            const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
+            uint32_t *n_hit = s->counters.p + n_cnt + 1 + (size_t)n_batches * (D + 1) + b;  // behind the fetch counters: not a segment count
+            k_prepare<<<div_up(tiles * 32u, kPrepThreads), kPrepThreads, 0, st>>>(W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done,
+                                                                                  s->hit_pix.p, n_hit, s->rng_start.p, hit_cap, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+            if (D > 1)
+                k_shade_first<<<(uint32_t)ctx->sm_count * 2u, kFirstThreads, 0, st>>>(sd, cd, W, H, S, phit, s->hit_pix.p, n_hit, s->rng_start.p, hit_cap,
+                                                                                      make_queue(s, 0, ref_mul), cnt + 2, s->ray_bins, fp->flags);
+            s->launches += 2;
             for (uint32_t d = 2; d <= D; d++) {
                 const Queue qin = make_queue(s, d & 1, ref_mul), qout = make_queue(s, (d + 1) & 1, ref_mul);
                 const ExtendIn in{qin.o, qin.d, nullptr};
@@ -1157,8 +1134,8 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
                     k_shade<512, false><<<shade_grid, 512, 0, st>>>(sd, qin, cnt + d, s->hit.p, qout, cnt + d + 1, s->result.p, d, D, bg, s->ray_bins, fp->flags);
                 s->launches += 1;
             }
-            const int fresh = (b == 0 && !(fp->flags & RT_FLAG_ACCUMULATE)) ? 1 : 0;
-            k_accumulate<<<div_up(npix, 256), 256, 0, st>>>(s->result.p, S, npix, reinterpret_cast<float4 *>(out->accum_linear), fresh);
+            // hit pixels: ordered sum of their S path results on top of what k_prepare left (fresh / previous sum)
+            if (D > 1) k_accumulate_hits<<<(uint32_t)ctx->sm_count * 8u, 256, 0, st>>>(s->result.p, s->hit_pix.p, n_hit, S, reinterpret_cast<float4 *>(out->accum_linear), fresh);
             s->launches += 1;
             done += S;
         }
