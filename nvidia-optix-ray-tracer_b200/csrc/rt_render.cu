@@ -318,22 +318,25 @@ k_primary_aov(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, const float4 *__r
 // sample (rng_start), so the samples are independent here: every lane has work (the per-pixel loop this replaces kept
 // 76 % of C4's lanes idle through 32 block-wide queue appends and wrote 3.2 GB of background colour per batch).
 // Path id = i * S + s: result[] holds hit pixels only and is summed in sample order by k_accumulate_hits.
-constexpr int kFirstThreads = 512;
-__global__ void __launch_bounds__(kFirstThreads)
+#ifndef RT_FIRST_LOG
+#define RT_FIRST_LOG 8
+#endif
+constexpr int kFirstThreads = 1 << RT_FIRST_LOG;
+__global__ void __launch_bounds__(kFirstThreads, 1024 / kFirstThreads)
 k_shade_first(SceneDev sc, CamDev cam, uint32_t W, uint32_t H, uint32_t S, const float4 *__restrict__ phit,
               const uint32_t *__restrict__ hit_pix, const uint32_t *__restrict__ n_hit, const uint32_t *__restrict__ rng_start,
               uint32_t cap, Queue out, uint32_t *out_count, uint32_t nb, uint32_t flags) {
     __shared__ uint32_t s_cnt[kFirstThreads / 32][kBins + 1];
     __shared__ uint32_t s_base[kBins];
     const uint32_t n = *n_hit;
-    // a block pass = 16 consecutive hit pixels x 32 samples (at S >= 32): the 16 lanes of a half warp read 64 contiguous bytes of
+    // a block pass = 8 consecutive hit pixels x 32 samples (256 threads, S >= 32): 8 lanes read one 32-byte sector of
     // every rng_start word, and all samples of a pixel enter the queue together, next to their neighbours' (rays that
     // start from the same hit point walk the same nodes: queueing sample-major over the whole frame cost 2.5 % of
     // the traversal time)
     // (fewer samples per launch: SP = the power of two >= min(S, 32) sample slots, 512 / SP pixels per pass)
     uint32_t sp_log = 0;
     while ((1u << sp_log) < S && sp_log < 5u) sp_log++;
-    const uint32_t pi_log = 9u - sp_log;  // kFirstThreads = 512
+    const uint32_t pi_log = (uint32_t)RT_FIRST_LOG - sp_log;
     const uint32_t il = threadIdx.x & ((1u << pi_log) - 1u), sl = threadIdx.x >> pi_log;
     const uint32_t n_groups = (n + (1u << pi_log) - 1u) >> pi_log, s_passes = (S + (1u << sp_log) - 1u) >> sp_log;
     for (uint32_t w = blockIdx.x; w < n_groups * s_passes; w += gridDim.x) {  // block-uniform trip count
@@ -1116,7 +1119,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             k_prepare<<<div_up(tiles * 32u, kPrepThreads), kPrepThreads, 0, st>>>(W, H, S, D, bg, phit, s->rng_cur.p, s->rng_pix_off.p, fp->seed, fp->sample_offset + done,
                                                                                   s->hit_pix.p, n_hit, s->rng_start.p, hit_cap, reinterpret_cast<float4 *>(out->accum_linear), fresh);
             if (D > 1)
-                k_shade_first<<<(uint32_t)ctx->sm_count * 2u, kFirstThreads, 0, st>>>(sd, cd, W, H, S, phit, s->hit_pix.p, n_hit, s->rng_start.p, hit_cap,
+                k_shade_first<<<(uint32_t)ctx->sm_count * (1024u / kFirstThreads), kFirstThreads, 0, st>>>(sd, cd, W, H, S, phit, s->hit_pix.p, n_hit, s->rng_start.p, hit_cap,
                                                                                       make_queue(s, 0, ref_mul), cnt + 2, s->ray_bins, fp->flags);
             s->launches += 2;
             for (uint32_t d = 2; d <= D; d++) {
