@@ -417,8 +417,20 @@ def run_ours(a):
             built_ev[k].record(on)
         built_for[k] = step
 
+    # e2e: the frame goes back to the host on its own stream while the next frame is already being built and rendered
+    # (the next frame's first kernels wait for the copy before anything can overwrite the frame buffer)
+    rb_stream, rb_ready, rb_done = torch.cuda.Stream(), torch.cuda.Event(), torch.cuda.Event()
+
+    def readback(src):
+        rb_ready.record(stream_obj)
+        with torch.cuda.stream(rb_stream):
+            rb_stream.wait_event(rb_ready)
+            h_rgba8.copy_(src, non_blocking=True)
+            rb_done.record(rb_stream)
+
     def frame(step, e2e, ahead=2):
         """`ahead` = how many further steps follow inside the same region (0, 1, 2+)"""
+        stream_obj.wait_event(rb_done)
         k = step % len(scs)
         if built_for[k] != step:
             launch_build(step, e2e, ahead >= 1, stream_obj)
@@ -432,7 +444,7 @@ def run_ours(a):
                                      split_primary=bool(a.split_primary), layout=a.stream_layout)
             rendered_ev[k].record(stream_obj)
             if rank == 0 and e2e:
-                h_rgba8.copy_(xch.frame, non_blocking=True)
+                readback(xch.frame)
             return
         # per-pixel XORWOW streams continue from frame to frame as in the reference (states are initialised
         # once, src/Global/RendererTime.cu:395): frame `step` owns samples [step*spp, (step+1)*spp)
@@ -442,7 +454,7 @@ def run_ours(a):
         if rank == 0:
             ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
             if e2e:
-                h_rgba8.copy_(rgba8, non_blocking=True)
+                readback(rgba8)
 
     def all_stats():
         sts = [x.stats() for x in scs]
@@ -468,6 +480,7 @@ def run_ours(a):
         for i in range(a.steps):
             frame(a.warmup + i, e2e, ahead=a.steps - 1 - i)
         pipe.drain()
+        stream_obj.wait_stream(rb_stream)   # the last frame has reached the host inside the timed region
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
