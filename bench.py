@@ -577,7 +577,7 @@ def run_ours(a):
             rl["measured_dram_frac_of_peak"] = (tj.get("dram_gbs") or 0.0) / peak
             rl["traffic_over_algorithmic"] = traffic / max(rl["algorithmic_bytes_per_launch"], 1.0)
         rl["measured_limiters"] = tj_note
-        rl["measured_bound"] = "SM ALU pipe (70 % busy) and instruction issue (70-72 %), not HBM: see measured_limiters" if tj_note else None
+        rl["measured_bound"] = "instruction issue (76-80 % of peak; ALU pipe 59-63 %), not HBM: see measured_limiters" if tj_note else None
         if world_size == 1 and not a.no_cpu_baseline:
             cb, oimg, (cw, ch, cspp) = cpu_sample(a, host, cam, a.cpu_seconds)
             line["cpu_baseline"] = cb
