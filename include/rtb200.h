@@ -128,19 +128,28 @@ int rt_abi_version(void);
  *      and the OptixInstance fill (RendererTime.cu:116-130, RendererMesh.cu:130-148) ---------- */
 int rt_scene_create(rt_context ctx, rt_scene *out);
 int rt_scene_destroy(rt_scene scene);
-/* Tuning knobs: "profile" (0/1: time every traversal launch with CUDA events), "wide" (1 = traverse
- * the 8-wide compressed BVH, default; 0 = the binary LBVH), "leaf_max" (primitives per leaf of
- * the binary tree: 1..8, 0 = 4; leaves of the 8-wide tree always hold one primitive), "batch_spp" (samples per pixel in flight per wavefront batch; 0 = auto: up to 32 within a third of free memory),
- * "t1" / "t2" / "t3" / "fetch_min" (warp-phase thresholds of the traversal kernel, results do not depend on
- * them), "extend_blocks_per_sm" (persistent grid size of the traversal kernel), "fused" (0, default: wavefront form, one closest-hit launch + one
- * shading launch per bounce over ray queues of 168 bytes per (pixel, sample) in flight; 1: ONE persistent kernel in which a lane follows a
- * path from its first scatter to its end, no queues: 40 bytes per (pixel, sample), 14 GB instead of 50 GB on the 4K / 10 M-sphere
- * workload at 0.96 of the throughput; bit-identical images), "chunk_spp" (fused form: samples per work unit), "compat_shading" (bit 0: sphere normals from the OBJECT-space centre
- * and radius as shader/Shader.cu:124-132 does although the hit point is in world space, bit 1: triangle vertex normals not rotated with
- * their instance as Shader.cu:139-142; default 0 = correct world-space shading), "ray_bins" (8 or 24: key of
- * the per-block grouping of scattered rays: octant, or octant x dominant axis), "shade_threads" (512 or
- * 1024), "refit_mode" (1 = shared-memory local climb + global top kernel, default; 0 = one kernel with
- * global counters).  None of them changes a result except "compat_shading". */
+/* Tuning knobs; none of them changes a result except "compat_shading":
+ *   "profile"              0/1: time every traversal launch with CUDA events (rt_stats.trace_ms)
+ *   "wide"                 1 (default) = traverse the 8-wide compressed BVH, 0 = the binary LBVH
+ *   "leaf_max"             primitives per leaf of the binary tree: 1..8, 0 = 4 (leaves of the 8-wide tree hold one primitive)
+ *   "batch_spp"            samples per pixel in flight per wavefront batch; 0 = auto: up to 32 within a third of free memory
+ *   "compact_queues"       1 (default) = wavefront queues sized from the frame's primary-hit count (rt_render waits for its
+ *                          primary-visibility pass, see rt_render); 0 = sized for every pixel, rt_render never blocks
+ *   "fused"                0 (default) = wavefront form: one closest-hit launch + one shading launch per bounce over ray
+ *                          queues (17.5 GB on the 4K / 10 M-sphere workload); 1 = ONE persistent kernel in which a lane
+ *                          follows a path from its first scatter to its end, no queues (14 GB, ~0.9 of the throughput);
+ *                          bit-identical images
+ *   "chunk_spp"            fused form: samples per work unit
+ *   "compat_shading"       bit 0: sphere normals from the OBJECT-space centre and radius as shader/Shader.cu:124-132 does
+ *                          although the hit point is in world space, bit 1: triangle vertex normals not rotated with their
+ *                          instance as Shader.cu:139-142 (SURVEY C quirks 1 and 2); default 0 = correct world-space shading
+ *   "t1" "t2" "t3" "fetch_min"   warp-phase thresholds of the traversal kernel
+ *   "extend_blocks_per_sm" persistent grid size of the traversal kernel (5..8, default 7)
+ *   "ray_bins"             8 or 24: key of the per-block grouping of scattered rays (octant, or octant x dominant axis)
+ *   "shade_threads"        256 (default), 512 or 1024: block size of the per-bounce shading kernel
+ *   "refit_mode"           1 (default) = shared-memory local climb + global top kernel, 0 = one kernel with global
+ *                          counters, 2 = range queries over a per-block sparse table + the same top kernel
+ *   "collapse_mode"        0 (default) = one thread per wide node, 1 = eight lanes per wide node */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 
 /* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz
