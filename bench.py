@@ -726,6 +726,10 @@ def run_c5(a):
 
     ctx = pkg.Context(local)
     sc = pkg.Scene(ctx)
+    # ray queues sized for every pixel here: with one process per GPU the per-frame read-back of the primary-hit count
+    # (option compact_queues, the default elsewhere) cost 8.6 ms of a 51 ms frame on eight GPUs (r7h/r7k: neither
+    # wake-up latency nor reallocation), and the 180 GB of a B200 hold the 54 GB this needs many times over
+    sc.set_option("compact_queues", 0)
     for kv in a.opt:
         k, v = kv.split("=")
         sc.set_option(k, int(v))

@@ -155,6 +155,8 @@ int rt_scene_destroy(rt_scene scene) {
     for (auto &e : s.ev)
         if (e) cudaEventDestroy(e);
     for (auto &e : s.prof_ev) cudaEventDestroy(e);
+    if (s.ev_hit) cudaEventDestroy(s.ev_hit);
+    if (s.h_hit) cudaFreeHost(s.h_hit);
     if (s.ev_fork) cudaEventDestroy(s.ev_fork);
     if (s.ev_join) cudaEventDestroy(s.ev_join);
     if (s.aux_stream) cudaStreamDestroy(s.aux_stream);

@@ -111,6 +111,7 @@ struct DevBuf {  // grow-only device buffer
     size_t cap = 0;
     cudaError_t reserve(size_t n, size_t *total_bytes) {
         if (n <= cap) return cudaSuccess;
+        const size_t had = cap;
         if (p) {
             cudaError_t e = cudaFree(p);
             if (e != cudaSuccess) return e;
@@ -118,7 +119,11 @@ struct DevBuf {  // grow-only device buffer
             p = nullptr;
             cap = 0;
         }
+        // first allocation: the request plus a little; a buffer that has to GROW again (per-frame sizes that drift, e.g. the
+        // hit-count-sized ray queues of a moving scene) grows by at least half, so that cudaFree + cudaMalloc — a device-wide
+        // synchronisation — happens a couple of times, not every frame
         size_t want = n + n / 16 + 64;
+        if (had) want = std::max(want, had + had / 2);
         cudaError_t e = cudaMalloc(&p, want * sizeof(T));
         if (e != cudaSuccess) return e;
         cap = want;
@@ -209,6 +214,8 @@ struct Scene {
     DevBuf<uint32_t> hit_pix;     // fused form: pixels whose primary ray hit something
     DevBuf<uint32_t> rng_start;   // fused form: [sample][6][npix] XORWOW state of stream(p, s) per hit pixel
     DevBuf<uint32_t> rng_pix_off; // sample offset the state of pixel p in rng_cur stands at (lazy stepping: only pixels that hit draw)
+    uint32_t *h_hit = nullptr;    // pinned word the primary-hit count is read back into (compact_queues)
+    cudaEvent_t ev_hit = nullptr;
     bool compact_queues = true;   // option "compact_queues": size the wavefront queues from the frame's primary-hit count (one stream sync per rt_render)
     bool fused = false;           // option "fused": one persistent path kernel instead of per-bounce wavefront launches
     uint32_t chunk_spp = 16;      // option "chunk_spp": samples per work unit of the fused kernel
