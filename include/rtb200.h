@@ -136,7 +136,7 @@ int rt_scene_destroy(rt_scene scene);
  *   "compact_queues"       1 (default) = wavefront queues sized from the frame's primary-hit count (rt_render waits for its
  *                          primary-visibility pass, see rt_render); 0 = sized for every pixel, rt_render never blocks
  *   "fused"                0 (default) = wavefront form: one closest-hit launch + one shading launch per bounce over ray
- *                          queues (17.5 GB on the 4K / 10 M-sphere workload); 1 = ONE persistent kernel in which a lane
+ *                          queues (16.3 GB on the 4K / 10 M-sphere workload); 1 = ONE persistent kernel in which a lane
  *                          follows a path from its first scatter to its end, no queues (14 GB, ~0.9 of the throughput);
  *                          bit-identical images
  *   "chunk_spp"            fused form: samples per work unit

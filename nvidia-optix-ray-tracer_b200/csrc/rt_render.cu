@@ -1072,7 +1072,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
             n_hit = *s->h_hit;
         }
         const size_t need = (size_t)std::max(n_hit, 1u) * std::min(Sb, spp);
-        const size_t qc = need + need / 8;  // head room: the hit count moves a little from frame to frame (buffers only grow)
+        const size_t qc = need + need / 32;  // a little head room; a scene whose hit count drifts further regrows by half (DevBuf)
         for (int k = 0; k < 2; k++) {
             RT_CUDA(ctx, s->q_o[k].reserve(k == 0 ? std::max(qc, (size_t)npix) : qc, &s->bytes));
             RT_CUDA(ctx, s->q_d[k].reserve(k == 0 ? std::max(qc, (size_t)npix) : qc, &s->bytes));
