@@ -295,6 +295,36 @@ int rt_accel_download_wide(rt_scene scene, float *wnodes_h, float *slot_geom_h, 
 int rt_trace_rays(rt_scene scene, const float *dev_rays, const uint32_t *dev_skip, size_t n,
                   float *dev_t, uint32_t *dev_id, void *stream);
 
+/* rt_trace_rays for callers that must not allocate.  No counterpart in the reference: optixTrace is only reachable
+ * from inside its pipeline, and the reference's host side allocates whenever it needs to (e.g. RendererImpl.cu:39-41).
+ *
+ * Who needs it: code that wants closest hits from an already built scene at a point where device allocation is off
+ * the table — a frame loop whose memory plan was frozen at start-up, a plugin inside a host application that owns
+ * the device allocator, a process sharing the GPU with something that has claimed the remaining memory (cudaMalloc
+ * would fail, or would stall every stream on the device while it runs).  rt_trace_rays grows scene-owned buffers
+ * with cudaMalloc when a batch is larger than any before it; this call never does.  It performs no cudaMalloc,
+ * cudaFree or other allocating call, whatever the batch size.
+ *
+ * Same arguments, same launches and bit-identical dev_t / dev_id as rt_trace_rays.  What differs is where the
+ * intermediate data lives (packed rays, skip slots, hit records, the traversal kernel's fetch counter): in a fixed
+ * array of 52 bytes per ray x RT_TRACE_STATIC_MAX_RAYS + 256 = 3.25 MiB that is part of the library image.  Every
+ * GPU that loads librtb200.so holds that array until the process exits, used or not.
+ *
+ * Limits and rules
+ *   - n <= RT_TRACE_STATIC_MAX_RAYS, otherwise RT_ERR_INVALID with a message naming the limit (split the batch).
+ *   - The scene must be built (rt_accel_build allocates; do that while allocation is still allowed).  With dev_skip
+ *     the id -> slot table is written into a buffer the build already owns, as rt_trace_rays does.
+ *   - One array per device, shared by all scenes, contexts and threads of the process.  It keeps whatever the previous
+ *     call left; the call clears the one word that must start at zero itself.  Calls whose GPU work can overlap
+ *     (different streams without an ordering between them) corrupt each other: keep them on one stream or order
+ *     them with events.
+ *   - The first call on each device looks up the array's device address (once, under a lock, with the context's
+ *     device current).  Make that first call — n = 0 is enough — before starting any stream capture.
+ *   - Option "profile" is ignored here (its event pool grows on demand). */
+#define RT_TRACE_STATIC_MAX_RAYS 65536
+int rt_trace_rays_static(rt_scene scene, const float *dev_rays, const uint32_t *dev_skip, size_t n,
+                         float *dev_t, uint32_t *dev_id, void *stream);
+
 /* ---- host-side maths of the path (pure CPU, no CUDA) ----------------------------------------
  * rt_camera_configure: SDL_GraphicsWindowConfigureCamera, src/GraphicsAPI/SDL_GraphicsWindow.cu:4-14
  *   (flip_up != 0 for every API except OpenGL).

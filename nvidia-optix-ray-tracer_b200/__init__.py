@@ -34,7 +34,9 @@ ABI_SYMBOLS = [
     "rt_accel_download", "rt_accel_download_wide", "rt_trace_rays", "rt_camera_configure", "rt_construct_transform",
     "rt_transform_time", "rt_transform_mesh", "rt_bake_color_ramp",
     "rt_spheres_advect", "rt_transforms_time", "rt_scene_set_transforms_device", "rt_render_primary", "rt_scene_set_primary_hits", "rt_peer_alloc", "rt_peer_free", "rt_peer_open", "rt_peer_close", "rt_resolve_parts",
+    "rt_trace_rays_static",
 ]
+RT_TRACE_STATIC_MAX_RAYS = 65536
 RT_MAX_PARTS = 16
 RT_PEER_HANDLE_BYTES = 64
 
@@ -121,6 +123,7 @@ def lib() -> C.CDLL:
         L.rt_accel_download.argtypes = [vp, vp, vp, vp, vp]
         L.rt_accel_download_wide.argtypes = [vp, vp, vp, vp, C.POINTER(u64)]
         L.rt_trace_rays.argtypes = [vp, vp, vp, sz, vp, vp, vp]
+        L.rt_trace_rays_static.argtypes = [vp, vp, vp, sz, vp, vp, vp]
         L.rt_camera_configure.argtypes = [f_p, f_p, f_p, C.c_int, C.POINTER(Camera)]
         L.rt_camera_configure.restype = None
         L.rt_construct_transform.argtypes = [f_p, f_p, f_p, f_p]
@@ -290,6 +293,10 @@ class Scene:
 
     def trace_rays(self, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream=None):
         self.ctx.check(lib().rt_trace_rays(self._h, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream))
+
+    def trace_rays_static(self, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream=None):
+        """rt_trace_rays through the library's fixed scratch array: allocates nothing, n <= RT_TRACE_STATIC_MAX_RAYS."""
+        self.ctx.check(lib().rt_trace_rays_static(self._h, rays_ptr, skip_ptr, n, t_ptr, id_ptr, stream))
 
     def stats(self) -> Stats:
         s = Stats()

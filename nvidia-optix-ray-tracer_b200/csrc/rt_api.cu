@@ -395,6 +395,12 @@ int rt_trace_rays(rt_scene scene, const float *dev_rays, const uint32_t *dev_ski
     return trace_rays(&scene->s, dev_rays, dev_skip, n, dev_t, dev_id, (cudaStream_t)stream);
 }
 
+int rt_trace_rays_static(rt_scene scene, const float *dev_rays, const uint32_t *dev_skip, size_t n, float *dev_t, uint32_t *dev_id, void *stream) {
+    if (!scene || (n && (!dev_rays || !dev_t || !dev_id))) return RT_ERR_INVALID;
+    DeviceGuard g(scene->s.ctx->device);
+    return trace_rays_static(&scene->s, dev_rays, dev_skip, n, dev_t, dev_id, (cudaStream_t)stream);
+}
+
 int rt_get_stats(rt_scene scene, rt_stats *out) {
     if (!scene || !out) return RT_ERR_INVALID;
     Scene &s = scene->s;

@@ -264,6 +264,8 @@ int resolve_parts(Context *ctx, const float *const *parts, int n_parts, size_t f
                   uint8_t *rgba8, cudaStream_t stream);
 int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id,
                cudaStream_t stream);
+int trace_rays_static(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id,
+                      cudaStream_t stream);
 SceneDev scene_dev(const Scene *s);
 int spheres_advect(Context *ctx, const float *base_c, const float *base_r, const float *vel, size_t n, float duration,
                    size_t frames, size_t frame, const float *pshift, const float *pscale, float *out_c, float *out_r,

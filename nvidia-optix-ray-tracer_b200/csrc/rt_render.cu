@@ -1303,4 +1303,92 @@ int trace_rays(Scene *s, const float *rays, const uint32_t *skip, size_t n, floa
     return RT_OK;
 }
 
+// ------------------------------------------------------------------ closest hits without any allocation
+// rt_trace_rays_static (rtb200.h): the same launches as trace_rays() above, but the packed ray queue, the skip
+// slots, the hit records and the fetch counter of the persistent traversal kernel live in ONE fixed array that is
+// part of the library image instead of in DevBuf storage grown with cudaMalloc.  Meant for hosts that are not
+// allowed to allocate at the moment they need a visibility query: a renderer thread inside a frame whose memory
+// budget was fixed at start-up, a plugin whose host application owns the allocator, a process sharing the GPU
+// with a job that has already taken the rest of the memory.
+//
+// g_trace_static is reserved on every device that loads librtb200.so, from load until the process exits.  All calls on a
+// device use the same bytes: two calls whose GPU work overlaps (different streams, different host threads,
+// different scenes) overwrite each other's rays and hits.  Contents persist between calls, so the one word that has
+// to start at zero — the fetch counter — is cleared on the stream before each use; every other byte a call
+// reads it has written itself first.
+constexpr size_t kStaticRays = RT_TRACE_STATIC_MAX_RAYS;
+constexpr size_t kStaticOffD = kStaticRays * sizeof(float4);                // packed directions + tmax
+constexpr size_t kStaticOffHit = 2 * kStaticRays * sizeof(float4);          // hit records
+constexpr size_t kStaticOffSkip = 3 * kStaticRays * sizeof(float4);         // skip slot per ray
+constexpr size_t kStaticOffFetch = kStaticOffSkip + kStaticRays * sizeof(uint32_t);  // fetch counter (own 256-byte line)
+constexpr size_t kStaticBytes = kStaticOffFetch + 256;
+static __device__ __align__(256) unsigned char g_trace_static[kStaticBytes];
+
+// In host code `g_trace_static` is only the handle the runtime registered for the symbol; the address the kernels need
+// is looked up once per device (with that device current) and kept here.
+constexpr int kStaticMaxDevices = 64;
+static unsigned char *g_trace_static_addr[kStaticMaxDevices] = {};
+static std::mutex g_trace_static_mu;
+
+static int trace_static_base(Context *ctx, unsigned char **base) {
+    int dev = -1;
+    RT_CUDA(ctx, cudaGetDevice(&dev));
+    if (dev != ctx->device) return set_error(ctx, RT_ERR_STATE, "rt_trace_rays_static: device %d is current, the context is bound to %d", dev, ctx->device);
+    if (dev < 0 || dev >= kStaticMaxDevices) return set_error(ctx, RT_ERR_UNSUPPORTED, "rt_trace_rays_static: device ordinal %d beyond %d", dev, kStaticMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_trace_static_mu);
+    if (!g_trace_static_addr[dev]) {
+        void *p = nullptr;
+        RT_CUDA(ctx, cudaGetSymbolAddress(&p, g_trace_static));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) return set_error(ctx, RT_ERR_CUDA, "rt_trace_rays_static: bad address for the static scratch array");
+        g_trace_static_addr[dev] = static_cast<unsigned char *>(p);
+    }
+    *base = g_trace_static_addr[dev];
+    return RT_OK;
+}
+
+int trace_rays_static(Scene *s, const float *rays, const uint32_t *skip, size_t n, float *t, uint32_t *id, cudaStream_t st) {
+    Context *ctx = s->ctx;
+    if (!s->built) return set_error(ctx, RT_ERR_STATE, "rt_trace_rays_static before rt_accel_build");
+    if (n > kStaticRays)
+        return set_error(ctx, RT_ERR_INVALID, "rt_trace_rays_static: %zu rays exceed the static scratch array (RT_TRACE_STATIC_MAX_RAYS = %zu); split the batch or use rt_trace_rays",
+                         n, kStaticRays);
+    // first call on this device: resolves the array's device address (do it before any stream capture)
+    unsigned char *base = nullptr;
+    const int rc0 = trace_static_base(ctx, &base);
+    if (rc0) return rc0;
+    if (!n) return RT_OK;
+    float4 *qo = reinterpret_cast<float4 *>(base);
+    float4 *qd = reinterpret_cast<float4 *>(base + kStaticOffD);
+    float4 *hit = reinterpret_cast<float4 *>(base + kStaticOffHit);
+    uint32_t *qskip = reinterpret_cast<uint32_t *>(base + kStaticOffSkip);
+    uint32_t *fetch = reinterpret_cast<uint32_t *>(base + kStaticOffFetch);
+    const SceneDev sd = scene_dev(s);
+    // gid -> slot map in vals[1], a buffer the build already owns (as in trace_rays)
+    if (skip && s->n_prims) {
+        k_invert_slots<<<div_up(s->n_prims, 256), 256, 0, st>>>(sd.slot_prim, s->n_prims, s->vals[1].p);
+        s->launches += 1;
+    }
+    k_pack_rays<<<div_up((uint32_t)n, 128), 128, 0, st>>>(rays, skip, s->vals[1].p, (uint32_t)n, qo, qd, qskip);
+    RT_CUDA(ctx, cudaMemsetAsync(fetch, 0, sizeof(uint32_t), st));
+    const ExtendIn in{qo, qd, qskip};
+    // the dispatch of launch_extend without its optional event timing (cudaEventCreate allocates)
+    const uint32_t grid = std::min((uint32_t)ctx->sm_count * s->extend_blocks_per_sm, std::max(1u, div_up((uint32_t)n, 128u)));
+    const int t1 = (int)s->t1, t2 = (int)s->t2, t3 = (int)s->t3, fm = (int)s->fetch_min;
+    if (!s->wide)
+        k_extend<<<grid, 128, 0, st>>>(sd, in, nullptr, (uint32_t)n, fetch, hit, t1, t2, fm);
+    else if (s->extend_blocks_per_sm >= 8)
+        k_extend_wide<8><<<grid, 128, 0, st>>>(sd, in, nullptr, (uint32_t)n, fetch, hit, t1, t2, t3, fm, RT_DEQ_MAGIC);
+    else if (s->extend_blocks_per_sm == 7)
+        k_extend_wide<7><<<grid, 128, 0, st>>>(sd, in, nullptr, (uint32_t)n, fetch, hit, t1, t2, t3, fm, RT_DEQ_MAGIC);
+    else if (s->extend_blocks_per_sm >= 6)
+        k_extend_wide<6><<<grid, 128, 0, st>>>(sd, in, nullptr, (uint32_t)n, fetch, hit, t1, t2, t3, fm, RT_DEQ_MAGIC);
+    else
+        k_extend_wide<5><<<grid, 128, 0, st>>>(sd, in, nullptr, (uint32_t)n, fetch, hit, t1, t2, t3, fm, RT_DEQ_MAGIC);
+    k_unpack_hits<<<div_up((uint32_t)n, 128), 128, 0, st>>>(sd, hit, (uint32_t)n, t, id);
+    s->launches += 3;
+    RT_CUDA(ctx, cudaGetLastError());
+    s->last_stream = st;
+    return RT_OK;
+}
+
 }  // namespace rtb
