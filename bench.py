@@ -517,13 +517,14 @@ def run_ours(a):
         trace_step = dv["trace_ms"] / a.steps                   # this rank's traversal-kernel time per step
         n_launch = max(1, int(st["trace_launches"]))
         achieved = seg_step * bseg / (trace_step * 1e-3) / 1e9 if trace_step > 0 else None
-        traffic, traffic_src, tj, tj_note = None, None, {}, None
+        traffic, traffic_src, tj, tj_note, issue_pct = None, None, {}, None, None
         try:  # measured DRAM bytes per traversal launch from the committed ncu --set full capture (same launch shape only)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_extend_wide"]
             tj_note = tj.get("limiters")
             same_shape = (a.n_spheres == 10_000_000 and a.width == 3840 and a.height == 2160 and a.depth == 5 and not a.batch_spp
                           and min(a.spp // world_size, 32) == tj.get("spp_in_flight"))
             if same_shape:
+                issue_pct = tj.get("issue_pct")
                 traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"] + " (%.0f GB/s of DRAM traffic over that launch: the L2 absorbs the rest)" % tj.get("dram_gbs", 0.0)
         except (OSError, KeyError, ValueError):
             pass
@@ -557,8 +558,17 @@ def run_ours(a):
             "build": {"mprims_per_s": n_prims / (dv["build_ms"] * 1e-3) / 1e6 if dv["build_ms"] > 0 else None, "ms": dv["build_ms"],
                       "n_prims": n_prims, "bytes_per_prim": 224,
                       "hbm_frac": (n_prims * 224 / (dv["build_ms"] * 1e-3) / 1e9 / peak) if dv["build_ms"] > 0 else None},
-            "roofline": {"bound": "hbm", "kernel": "k_extend_wide (BVH traversal, primary + bounce launches)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+            # bound / achieved / peak / frac are on the axis ncu measured as the limiter (issue slots of the SM sub-partitions,
+            # from the committed capture of this launch shape: null for any other shape); the SURVEY 8d bytes-per-segment
+            # model over the live launch time is kept beside it as algorithmic_gbs / algorithmic_frac (= model_frac)
+            "roofline": {"bound": "issue", "kernel": "k_extend_wide (BVH traversal, primary + bounce launches)",
+                         "achieved": issue_pct, "peak": 100.0 if issue_pct else None,
+                         "unit": "% of issue slots busy (smsp__issue_active, ncu capture of the same launch shape)",
+                         "frac": (issue_pct / 100.0) if issue_pct else None,
+                         "lanes_per_instruction": tj.get("lanes_per_inst") if issue_pct else None,
+                         "algorithmic_gbs": achieved, "algorithmic_frac": (achieved / peak) if achieved else None,
+                         "model_frac": (achieved / peak) if achieved else None, "hbm_peak_gbs": peak,
+                         "traffic": traffic,
                          "traffic_unit": "DRAM bytes per launch (ncu)", "traffic_source": traffic_src,
                          "algorithmic_bytes_per_launch": seg_step * a.steps / n_launch * bseg,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
@@ -578,6 +588,7 @@ def run_ours(a):
             rl["traffic_over_algorithmic"] = traffic / max(rl["algorithmic_bytes_per_launch"], 1.0)
         rl["measured_limiters"] = tj_note
         rl["measured_bound"] = "instruction issue (76-80 % of peak; ALU pipe 59-63 %), not HBM: see measured_limiters" if tj_note else None
+        line["build"]["bound"] = "latency / issue (ncu profiles/r4f_build_kernels_ncu.txt: only k_gather is DRAM-bound); hbm_frac is the 224 B/prim model over the measured time"
         if world_size == 1 and not a.no_cpu_baseline:
             cb, oimg, (cw, ch, cspp) = cpu_sample(a, host, cam, a.cpu_seconds)
             line["cpu_baseline"] = cb
@@ -828,8 +839,11 @@ def run_c5(a):
                       "note": "per-rank figure from rank 0's last build; every rank rebuilds its own frame concurrently",
                       "n_prims": n_prims, "bytes_per_prim": 224,
                       "hbm_frac": (n_prims * 224 / (dv["build_ms"] * 1e-3) / 1e9 / peak) if dv["build_ms"] > 0 else None},
-            "roofline": {"bound": "hbm", "kernel": "k_extend_wide (BVH traversal)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+            # no ncu capture of this launch shape is committed: the measured axis stays null, the model figure is labelled as such
+            "roofline": {"bound": "issue", "kernel": "k_extend_wide (BVH traversal)", "achieved": None, "peak": None,
+                         "unit": "% of issue slots busy (no capture of this workload committed; C4 capture: profiles/r7d)", "frac": None, "traffic": None,
+                         "algorithmic_gbs": achieved, "algorithmic_frac": (achieved / peak) if achieved else None,
+                         "model_frac": (achieved / peak) if achieved else None, "hbm_peak_gbs": peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                          "bytes_per_segment": bseg, "segments_per_launch": seg_step * a.steps / n_launch,
                          "avg_launch_ms": dv["trace_ms"] / n_launch, "trace_ms_per_step": trace_step,
