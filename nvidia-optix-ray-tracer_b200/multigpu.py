@@ -184,8 +184,12 @@ class PeerExchange:
         ordered only when both are the same stream (rtb200.h, rt_resolve_parts).  Anything else would let a peer
         read a buffer before its producer has finished: refuse it."""
         import torch
-        if stream is not None and int(stream) != int(torch.cuda.current_stream().cuda_stream):
-            raise ValueError("PeerExchange: pass torch's current stream (or None) - the NCCL fences run on it")
+        # None = the legacy default stream (handle 0) on the C-ABI side: ordered with the fences only while torch's
+        # current stream is that stream too, not inside a torch.cuda.stream(side_stream) block
+        handle = 0 if stream is None else int(stream)
+        if handle != int(torch.cuda.current_stream().cuda_stream):
+            raise ValueError("PeerExchange: pass torch's current stream (None only while torch's default stream is current)"
+                             " - the NCCL fences run on it")
 
     def fence(self):
         """Every rank's work enqueued so far is complete before anything enqueued after this runs

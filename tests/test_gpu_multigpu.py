@@ -152,3 +152,21 @@ def test_two_rank_peer_exchange_is_bit_exact(tmp_path, pkg, synth):
         wu = np.array([orc.color_to_uchar4(total[i, :3] * k) for i, k in zip(idx, inv)])
         assert np.abs(got[idx].astype(int) - wu.astype(int)).max() <= 1
     gs.close()
+
+
+def test_peer_exchange_refuses_unordered_streams():
+    """stream=None means the legacy default stream on the C-ABI side; the fences run on torch's current stream.  The two
+    are ordered only while torch's default stream is current: inside a side-stream block None must be refused, the
+    side stream's own handle accepted."""
+    import torch
+    mg = importlib.import_module("nvidia-optix-ray-tracer_b200.multigpu")
+    x = mg.PeerExchange.__new__(mg.PeerExchange)   # _check_stream uses no state
+    x._check_stream(None)
+    x._check_stream(torch.cuda.current_stream().cuda_stream)
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        x._check_stream(side.cuda_stream)
+        with pytest.raises(ValueError):
+            x._check_stream(None)
+    with pytest.raises(ValueError):
+        x._check_stream(side.cuda_stream)
