@@ -147,13 +147,21 @@ int rt_scene_destroy(rt_scene scene);
  *   "extend_blocks_per_sm" persistent grid size of the traversal kernel (5..8, default 7)
  *   "ray_bins"             8 or 24: key of the per-block grouping of scattered rays (octant, or octant x dominant axis)
  *   "shade_threads"        256 (default), 512 or 1024: block size of the per-bounce shading kernel
+ *   "rng_max_lag"          0..2048 samples, default 96: a frame whose sample_offset lies further ahead of the scene's per-pixel
+ *                          stream states than this re-creates all states in one launch instead of stepping each hit pixel's
+ *                          state forward (break-even measured at 4K: 92 samples, profiles/r9c_rng_lag.txt); same samples either way
  *   "refit_mode"           1 (default) = shared-memory local climb + global top kernel, 0 = one kernel with global
  *                          counters, 2 = range queries over a per-block sparse table + the same top kernel
  *   "collapse_mode"        0 (default) = one thread per wide node, 1 = eight lanes per wide node */
 int rt_scene_set_option(rt_scene scene, const char *name, int64_t value);
 
 /* Material tables: roughs = float[n][3] albedo; metals = float[m][4] albedo + fuzz
- * (HitGroupParams.rough/metal, Shader.cuh:57-69).  Host or device pointers. */
+ * (HitGroupParams.rough/metal, Shader.cuh:57-69).  Host or device pointers.
+ * Call it BEFORE rt_accel_build: the build checks every instance's material range (mat_index + k*mat_stride) against
+ * the tables as they stand at that moment and fails with RT_ERR_INVALID for a scene whose tables are still empty.
+ * Replacing the tables afterwards by ones with at least as many entries needs no rebuild (the values are read at
+ * render time); a table that gets SMALLER invalidates the build: rt_render returns RT_ERR_STATE until
+ * rt_accel_build has run (and re-checked the ranges) again. */
 int rt_scene_set_materials(rt_scene scene, const float *roughs, size_t n_rough,
                            const float *metals, size_t n_metal);
 
@@ -215,7 +223,7 @@ int rt_spheres_advect(rt_context ctx, const float *dev_base_centers, const float
  *      positions / velocities float[3n], quaternions float[4n] {x,y,z,w} (16-byte aligned); output float[12n]
  *      row-major 3x4 (16-byte aligned), ready for rt_scene_set_transforms_device.  Same operation order as
  *      rt_transform_time: the translation column is bit-identical to it; the rotation entries go through the CUDA
- *      libm's sinf/cosf/acosf/asinf/atan2f instead of glibc's and differ by <= 4e-6 absolute (tests/test_gpu_build.py).
+ *      libm's sinf/cosf/acosf/asinf/atan2f instead of glibc's and differ by <= 4e-6 absolute (tests/test_gpu_advect.py).
  *      Parity configs (C1-C3) therefore keep rt_transform_time on the host; this is the at-scale path. */
 int rt_transforms_time(rt_context ctx, const float *dev_positions, const float *dev_velocities,
                        const float *dev_quat_cur, const float *dev_quat_next, size_t n, float duration,

@@ -133,6 +133,7 @@ int rt_scene_set_option(rt_scene scene, const char *name, int64_t value) {
     else if (k == "collapse_mode") { s.collapse_mode = (uint32_t)std::min<int64_t>(1, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "refit_mode") { s.refit_mode = (uint32_t)std::min<int64_t>(2, std::max<int64_t>(0, value)); s.built = false; }
     else if (k == "extend_blocks_per_sm") s.extend_blocks_per_sm = (uint32_t)std::min<int64_t>(32, std::max<int64_t>(1, value));
+    else if (k == "rng_max_lag") s.rng_max_lag = (uint32_t)std::min<int64_t>(2048, std::max<int64_t>(0, value));
     else return set_error(s.ctx, RT_ERR_INVALID, "unknown option '%s'", name);
     return RT_OK;
 }
@@ -177,6 +178,9 @@ int rt_scene_set_materials(rt_scene scene, const float *roughs, size_t n_rough, 
         RT_CUDA(ctx, cudaMemcpy2D(s.d_roughs.p, sizeof(float4), roughs, 3 * sizeof(float), 3 * sizeof(float), n_rough, cudaMemcpyDefault));
     }
     if (n_metal) RT_CUDA(ctx, cudaMemcpy(s.d_metals.p, metals, n_metal * sizeof(float4), cudaMemcpyDefault));
+    // rt_accel_build checked every instance's material range against the tables as they stood then; a table that
+    // shrinks could leave indices pointing at stale rows of the grow-only buffers, so the check has to run again
+    if (n_rough < s.n_rough || n_metal < s.n_metal) s.built = false;
     s.n_rough = n_rough;
     s.n_metal = n_metal;
     return RT_OK;

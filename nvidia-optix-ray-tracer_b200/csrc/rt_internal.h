@@ -227,6 +227,9 @@ struct Scene {
     uint32_t extend_blocks_per_sm = 7;
     uint32_t ray_bins = 8, shade_threads = 256;  // queue grouping of scattered rays (rt_render.cu binned_push)
     uint32_t collapse_mode = 0;   // 0: k_collapse (one thread per wide node); 1: k_collapse8 (eight lanes per wide node)
+    // samples: a frame further ahead of the per-pixel stream states than this re-creates them (k_rng_init, +1.4 ms at 4K)
+    // instead of stepping every hit pixel's state (0.0155 ms per sample of gap at 4K): break-even 92, profiles/r9c_rng_lag.txt
+    uint32_t rng_max_lag = 96;
     uint32_t refit_mode = 1;      // 0: one kernel, global counters; 1: k_refit_local (shared-memory climb) + k_refit_top; 2: k_refit_rmq (range queries) + k_refit_top
     DevBuf<uint32_t> counters;    // queue counters
     DevBuf<unsigned long long> seg_total;

@@ -437,7 +437,7 @@ k_shade(SceneDev sc, Queue in, const uint32_t *__restrict__ in_count, const floa
     }
 }
 
-// ==================================================================== fused path kernel (option "fused", default)
+// ==================================================================== fused path kernel (option "fused" = 1; the default is the wavefront form)
 // The reference's recursion (optixTrace inside closest-hit, Shader.cu:229-241) as ONE persistent kernel: a lane
 // owns a path from its first scatter to its end — closest hit over the 8-wide tree, then the closest-hit / miss
 // program, then the next segment — so no ray queues, no hit records and no per-bounce launches (and drains of
@@ -901,7 +901,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
     // samples per pixel in flight per wavefront batch: larger batches amortise the drain of the persistent
     // traversal grid (C4: 4 -> 32 spp per batch = +5 %); 168 bytes of queue per (pixel, sample).  Auto: up to
     // 32, within a third of the free device memory (and 48 GB).  Results do not depend on it.
-    // Fused form (option "fused", default; needs the 8-wide tree): no queues.  Per batch of Sb samples: 16 bytes of
+    // Fused form (option "fused" = 1, not the default; needs the 8-wide tree): no queues.  Per batch of Sb samples: 16 bytes of
     // result and 24 bytes of stream state per (pixel, sample), sized for the worst case (every pixel hits).
     const bool fused = s->fused && s->wide;
     const uint32_t chunk = std::max(1u, s->chunk_spp);
@@ -1010,7 +1010,7 @@ int render_frame(Scene *s, const rt_camera *cam, const rt_frame_params *fp, cons
         // A new seed / size, a request behind the states or far ahead of them re-creates all of them at this launch's
         // first sample (k_rng_init, ~1 ms at 4K) rather than leaving it to the per-pixel curand_init of the kernels.
         const bool same = s->rng_valid && s->rng_seed == fp->seed && s->rng_w == W && s->rng_h == H;
-        const bool reinit = !same || (uint64_t)fp->sample_offset < s->rng_cur_off || (uint64_t)fp->sample_offset - s->rng_cur_off > kRngMaxLag;
+        const bool reinit = !same || (uint64_t)fp->sample_offset < s->rng_cur_off || (uint64_t)fp->sample_offset - s->rng_cur_off > std::min(s->rng_max_lag, kRngMaxLag);
         if (reinit) {
             if (!s->aux_stream) {
                 RT_CUDA(ctx, cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));

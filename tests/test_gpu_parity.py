@@ -142,6 +142,27 @@ def test_spp_partition_and_accumulate_flag(pkg, synth):
     gs.close()
 
 
+@pytest.mark.parametrize("lag", [0, 96, 2048])
+def test_sample_gap_policy_does_not_change_the_samples(pkg, synth, lag):
+    """A frame 150 samples ahead of where the per-pixel streams stand: stepping the states (rng_max_lag >= gap) and
+    re-creating them (rng_max_lag < gap) give the frame a fresh scene renders at that offset, bit for bit."""
+    d = scenes.random_scene(pkg, synth, 3000, seed=4, metal_every=5)
+    cam = pkg.camera_configure([2.2, 0, 0.1], [0, 0, 1e-3], [0, 0, 1], False)
+    fresh = scenes.GpuScene(pkg, d)
+    want = fresh.render(cam, 160, 96, 4, 5, 11, sample_offset=154)
+    fresh.close()
+    gs = scenes.GpuScene(pkg, d, options={"rng_max_lag": lag})
+    gs.render(cam, 160, 96, 4, 5, 11, sample_offset=0)
+    got = gs.render(cam, 160, 96, 4, 5, 11, sample_offset=154)
+    assert np.array_equal(got["accum"].view(np.uint32), want["accum"].view(np.uint32))
+    back = gs.render(cam, 160, 96, 4, 5, 11, sample_offset=2)   # behind the states: always re-created
+    again = scenes.GpuScene(pkg, d)
+    ref = again.render(cam, 160, 96, 4, 5, 11, sample_offset=2)
+    assert np.array_equal(back["accum"].view(np.uint32), ref["accum"].view(np.uint32))
+    again.close()
+    gs.close()
+
+
 def test_time_mode_instances_rebuild_per_frame(pkg, synth, oracle):
     """Per-frame flow of RendererTime::startRender: update instance transforms, rebuild, render."""
     fr = scenes.load_particle_frame0()

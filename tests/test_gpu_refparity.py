@@ -101,3 +101,44 @@ def test_material_index_out_of_range_is_rejected(pkg, synth):
     sc.build()
     sc.close()
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_materials_after_build_and_shrinking_tables(pkg, synth):
+    """the range check lives in rt_accel_build, so (a) a build before any rt_scene_set_materials fails against the
+    empty tables (documented order), (b) equal-size tables set after a build need no rebuild, (c) a table that shrinks
+    after a build invalidates it: render is refused until the build has re-checked, and the re-check fails."""
+    import torch
+    ctx = pkg.Context(0)
+    sc = pkg.Scene(ctx)
+    c = torch.zeros((8, 3), device="cuda")
+    c[:, 0] = torch.arange(8, device="cuda") * 0.3
+    r = torch.full((8,), 0.1, device="cuda")
+    g = sc.add_spheres(c.data_ptr(), r.data_ptr(), 8)
+    sc.add_instance(g, None, pkg.RT_MAT_ROUGH, 0, 1)      # indices 0..7
+    with pytest.raises(pkg.RtError, match="table of 0 entries"):
+        sc.build()
+    roughs = np.full((8, 3), 0.5, np.float32)
+    sc.set_materials(roughs.ctypes.data, 8, None, 0)
+    sc.build()
+    cam = pkg.camera_configure([1.0, -3.0, 0.0], [1.0, 0, 0], [0, 0, 1], False)
+    acc = torch.zeros((32 * 16, 4), device="cuda")
+
+    def render():
+        sc.render(cam, 32, 16, 1, 5, 7, (0.7, 0.8, 0.9), 0, 0, acc.data_ptr(), None, None, None, None)
+        torch.cuda.synchronize()
+
+    render()
+    roughs2 = np.full((8, 3), 0.25, np.float32)
+    sc.set_materials(roughs2.ctypes.data, 8, None, 0)     # same size: still built
+    render()
+    sc.set_materials(roughs2.ctypes.data, 5, None, 0)     # smaller: indices 5..7 would read stale rows
+    with pytest.raises(pkg.RtError, match="before rt_accel_build"):
+        render()
+    with pytest.raises(pkg.RtError, match="material index"):
+        sc.build()
+    sc.set_materials(roughs2.ctypes.data, 8, None, 0)
+    sc.build()
+    render()
+    sc.close()
+    ctx.close()
