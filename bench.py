@@ -541,7 +541,7 @@ def run_ours(a):
                                                                       if xch is not None else "NCCL reduce + resolve on rank 0")) if world_size > 1 else "single GPU",
                        "l2": "inputs larger than L2 (primitives + BVH %.0f MB; with ray queues / path state %.0f MB on the device)" % (scene_bytes / 1e6, st["device_bytes"] / 1e6),
                        "streams": ("single rank: frame f = samples [f*spp, (f+1)*spp) of every pixel's stream" if world_size == 1 else
-                                   ("rank r walks its own region of every pixel's stream (no per-frame re-positioning)" if a.stream_layout == "rank"
+                                   ("rank r walks its own region of every pixel's stream (no per-frame re-positioning): statistically equivalent to, not sample-identical with, the 1-GPU frame of the same seed (layout 'frame' is)" if a.stream_layout == "rank"
                                     else "frame f = samples [f*spp, (f+1)*spp), split over the ranks (states re-positioned every frame)")),
                        "step": "LBVH rebuild + render + resolve" + (" (two scenes: the rebuild of step i+1 overlaps the render of step i)" if pipelined else ""),
                        "primary_rays": "traced once per pixel (no jitter in the reference), counted once" +
@@ -607,6 +607,30 @@ def run_ours(a):
                                     "segments_equal": bool(int(sc.stats().segments) == int(oimg["segments"]))}
         else:
             line["cpu_baseline"] = None
+        if world_size == 1 and a.depth <= 5:
+            # the same step in the one mode that is bit-exact with the reference's own shader/Shader.cu:94-242 (compat_shading = 3 +
+            # both REF transport flags, tests/test_gpu_refparity.py): what reference-exactness costs against the default flags
+            ref_flags = pkg.RT_FLAG_REF_NO_SELF_SKIP | pkg.RT_FLAG_REF_MUL_ON_RETURN
+            sc.set_option("compat_shading", 3)
+            n_ref = max(2, min(a.steps, 6))
+            seg0, t0, t1 = 0, torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            for i in range(2 + n_ref):
+                if i == 2:
+                    torch.cuda.synchronize()
+                    seg0 = int(sc.stats().segments_total)
+                    t0.record()
+                sc.build(stream)
+                sc.render(cam, a.width, a.height, a.spp, a.depth, a.seed, (0.7, 0.8, 0.9), i * a.spp, ref_flags, accum.data_ptr(), None, None, None, stream)
+                ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
+            t1.record()
+            torch.cuda.synchronize()
+            ref_ms = t0.elapsed_time(t1) / n_ref
+            ref_segs = (int(sc.stats().segments_total) - seg0) / n_ref
+            line["ref_exact"] = {"mode": "compat_shading=3 + RT_FLAG_REF_NO_SELF_SKIP | RT_FLAG_REF_MUL_ON_RETURN (bit-exact with shader/Shader.cu)",
+                                 "ms_per_step": ref_ms, "value": ref_segs / (ref_ms * 1e-3) / 1e6, "unit": "Mrays/s", "steps": n_ref,
+                                 "segments_per_step": ref_segs, "ms_over_default": ref_ms / (dv["ms"] / a.steps),
+                                 "note": "a different random walk (no self-exclusion) and a uint4 of albedos per queue entry: segment counts differ from the default step"}
+            sc.set_option("compat_shading", 0)
     if world_size > 1:
         # correctness of the N-rank frame: one more frame through the exchange, then rank 0 renders the same samples
         # alone and compares the two RGBA8 frames (partial sums are re-associated: expect <= 1 LSB)

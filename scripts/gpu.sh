@@ -15,6 +15,8 @@
 #   ab        A/B of library builds: each remaining argument is "LIBSUFFIX|bench args" (LIBSUFFIX "" = librtb200.so,
 #             "cs" = librtb200_cs.so built with make -C csrc OUT=../librtb200_cs.so EXTRA=-D...), one short bench each
 #   libtest   SUFFIX: the GPU parity tests against librtb200_SUFFIX.so
+#   cubsort   library yardstick for the sort stage: cub::DeviceRadixSort::SortPairs on 10 M and 99.7 M (key, id) pairs
+#             (scripts/yardstick/cub_sort.cu, scratch binary in build/, never part of the product)
 set -u
 JOB=${1:-check}; TAG=${2:-run}; shift 2 2>/dev/null || true
 O=gpurun_out; mkdir -p $O
@@ -30,6 +32,11 @@ for l in open(sys.argv[1]):
 EOF
 }
 case $JOB in
+cubsort)
+  mkdir -p build
+  nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a scripts/yardstick/cub_sort.cu -o build/cub_sort && \
+  (build/cub_sort 10000010; build/cub_sort 99700000) > $O/${TAG}_cub_sort.txt 2>&1; echo "rc=$?"; cat $O/${TAG}_cub_sort.txt
+  ;;
 check)
   nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/${TAG}_smi.txt
   timeout 300 python __graft_entry__.py smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $O/${TAG}_smoke.log
