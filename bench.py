@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-build-100m", action="store_true", help="skip the C5-size LBVH build entry of the default line")
+    ap.add_argument("--no-c5", action="store_true", help="skip the bounded BASELINE config 5 entry (99.7 M spheres, frame-parallel) of the default line")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--leaf-max", type=int, default=0)
     ap.add_argument("--batch-spp", type=int, default=0)
@@ -652,6 +653,22 @@ def run_ours(a):
             line["parity_check"] = {"against": "the same sample blocks rendered by rank 0 alone", "pixels": npix, "stream_layout": a.stream_layout,
                                     "rgba8_max_abs_diff": int(diff.max().item()), "rgba8_pixels_differing": int((diff.amax(dim=1) > 0).sum().item())}
         dist.barrier()
+    if not a.no_c5:
+        # BASELINE config 5, bounded, on every rank (frame-parallel: no exchange), after the C4 scenes have given their memory back
+        for x in scs:
+            x.close()
+        scs = []
+        torch.cuda.empty_cache()
+        c5 = None
+        try:
+            c5 = c5_leg(pkg, synth, torch, dist, dev, ctx, stream, rank, world_size, seed=a.seed,
+                        parity_rays=8 if (world_size == 1 and not a.no_cpu_baseline) else 0)
+        except Exception as e:  # noqa: BLE001 - the headline number must still be printed
+            if world_size > 1:
+                raise               # a rank that drops out would leave the others in the leg's barrier
+            c5 = {"error": repr(e)}
+        if rank == 0:
+            line["c5"] = c5
     if rank == 0:
         if world_size == 1 and not a.no_build_100m:
             for x in scs:
@@ -724,6 +741,90 @@ def c5_parity(a, pkg, synth, torch, ctx, sc, d_base_c, d_base_r, d_vel, d_c, d_r
     return {"against": "CPU oracle brute force over every sphere of frame %d" % f, "n_prims": int(n), "primary_rays": int(n_rays),
             "primary_hits": int(hit.sum()), "primary_mismatch": bad, "scattered_rays": int(len(rays2)),
             "scattered_hits": int((oi2 != 0xFFFFFFFF).sum()), "scattered_mismatch": bad2, "oracle_seconds": round(time.time() - t0, 1)}
+
+
+def terrain_ramp_torch(torch, count, device):
+    """terrain_ramp_numpy on the device (float32 torch): the 99.7 M-row material table of the C5 leg is 1.2 GB and is
+    not worth a host round trip; colours do not change a segment count."""
+    u = torch.arange(count, device=device, dtype=torch.float32) / float(max(count - 1, 1))
+    pos = torch.tensor([p for p, _ in TERRAIN_STOPS], device=device, dtype=torch.float32)
+    col = torch.tensor([c for _, c in TERRAIN_STOPS], device=device, dtype=torch.float32)
+    hi = torch.searchsorted(pos, u, right=False).clamp_(1, len(TERRAIN_STOPS) - 1)
+    lo = hi - 1
+    t = ((u - pos[lo]) / (pos[hi] - pos[lo])).clamp_(0.0, 1.0)
+    return (col[lo] + (col[hi] - col[lo]) * t[:, None]).contiguous()
+
+
+def c5_leg(pkg, synth, torch, dist, dev, ctx, stream, rank, world_size, warm=2, frames=4, spp=16, depth=5, width=3840, height=2160,
+           seed=1, parity_rays=0):
+    """Bounded BASELINE config 5 entry of the default line, at every N: the 99.7 M-sphere packing generated
+    on the device, then per rank `warm` + `frames` frames of the frame-parallel loop of run_c5 (frame = step * world + rank:
+    rt_spheres_advect -> rt_accel_build -> rt_render 16 spp at 4K -> rt_resolve), no data-path collective, weak scaling.
+    Device-resident timing (CUDA events, max over ranks); `bench.py --workload c5` is the full arm with host inputs."""
+    dt, frames_total = 0.01, 256
+    base_c, base_r, vel = synth.hcp_spheres_device(torch, 100_000_000, dev)
+    n = int(base_r.numel())
+    d_c, d_r = torch.empty_like(base_c), torch.empty_like(base_r)
+    ramp = terrain_ramp_torch(torch, n, dev)
+    npix = width * height
+    accum = torch.zeros((npix, 4), dtype=torch.float32, device=dev)
+    rgba8 = torch.zeros((npix, 4), dtype=torch.uint8, device=dev)
+    sc = pkg.Scene(ctx)
+    sc.set_option("compact_queues", 0)   # as run_c5: no per-frame read-back with one process per GPU
+    metals = np.float32([[0.8, 0.85, 0.88, 0.0]])
+    sc.set_materials(ramp.data_ptr(), n, metals.ctypes.data, 1)
+    g_s = sc.add_spheres(d_c.data_ptr(), d_r.data_ptr(), n)
+    sc.add_instance(g_s, None, pkg.RT_MAT_ROUGH, 0, 1)
+
+    def frame(step):
+        f = (step * world_size + rank) % frames_total
+        ctx.spheres_advect(base_c.data_ptr(), base_r.data_ptr(), vel.data_ptr(), n, dt * frames_total, frames_total, f,
+                           [0.0, 0.0, 0.0], [1.0, 1.0, 1.0], d_c.data_ptr(), d_r.data_ptr(), stream)
+        sc.build(stream)
+        cam = pkg.camera_configure(**synth.c5_camera(f, dt))
+        sc.render(cam, width, height, spp, depth, seed, (0.7, 0.8, 0.9), f * spp, 0, accum.data_ptr(), None, None, None, stream)
+        ctx.resolve(accum.data_ptr(), npix, None, rgba8.data_ptr(), stream)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(warm):
+        frame(i)
+    barrier()
+    st0 = sc.stats()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(frames):
+        frame(warm + i)
+    e1.record()
+    barrier()
+    st1 = sc.stats()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    sg = torch.tensor([float(st1.segments_total - st0.segments_total)], device=dev, dtype=torch.float64)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sg, op=dist.ReduceOp.SUM)
+    ms, segs = float(t.item()), float(sg.item())
+    out = {"workload": f"C5 synthetic {n} sphere jittered-HCP DEM packing (phi 0.55, generated on the device), 256-frame series dt=0.01, "
+                       f"{width}x{height}, {spp} spp, depth {depth}; per rank {warm} warm + {frames} timed frames",
+           "n_gpus": world_size, "scaling": "weak", "parallelism": f"frame-parallel x{world_size} (frame = step*{world_size}+rank), no data-path collective",
+           "step": "per rank: rt_spheres_advect + LBVH rebuild + render + resolve of one frame", "steps": frames, "warmup": warm,
+           "ms_per_step": ms / frames, "frames_per_s": world_size * frames / (ms * 1e-3), "value": segs / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
+           "segments_per_frame": segs / (world_size * frames), "rebuild_ms": float(st1.build_ms),
+           "rebuild_mprims_per_s": n / (float(st1.build_ms) * 1e-3) / 1e6 if st1.build_ms > 0 else None,
+           "aggregate_rebuild_mprims_per_s": world_size * n / (float(st1.build_ms) * 1e-3) / 1e6 if st1.build_ms > 0 else None,
+           "device_bytes": int(st1.device_bytes), "gpu_launches": int(st1.kernel_launches - st0.kernel_launches) * world_size,
+           "timing": "device-resident: CUDA events around the timed frames, max over ranks (rank 0's rebuild_ms); inputs never leave the device in this leg"}
+    if parity_rays and rank == 0:
+        from types import SimpleNamespace
+        out["parity_check"] = c5_parity(SimpleNamespace(width=width, height=height), pkg, synth, torch, ctx, sc, base_c, base_r, vel, d_c, d_r, n,
+                                        dt, frames_total, stream, n_rays=parity_rays)
+    sc.close()
+    del base_c, base_r, vel, d_c, d_r, ramp, accum, rgba8
+    torch.cuda.empty_cache()
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------

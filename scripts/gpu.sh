@@ -20,7 +20,7 @@
 set -u
 JOB=${1:-check}; TAG=${2:-run}; shift 2 2>/dev/null || true
 O=gpurun_out; mkdir -p $O
-SHORT="python bench.py --steps 1 --warmup 1 --spp 8 --no-cpu-baseline"
+SHORT="python bench.py --steps 1 --warmup 1 --spp 8 --no-cpu-baseline --no-c5"
 brief() { python - "$1" <<'EOF'
 import json, sys
 for l in open(sys.argv[1]):
@@ -48,7 +48,7 @@ bench)
   timeout 900 python bench.py "$@" > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"; brief $O/${TAG}_bench.json; tail -2 $O/${TAG}_bench.err
   ;;
 launches)
-  CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline $*"
+  CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-c5 $*"
   timeout 600 $CMD > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err && \
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${TAG}_launches.csv $CMD > $O/${TAG}_ncu.log 2>&1
   echo "rc=$?"; brief $O/${TAG}_bench.json
