@@ -289,3 +289,46 @@ def ref_pin_cases(pkg, synth):
     inst = instanced_scene(pkg, synth)
     return [("c1_compat", c1, cam1, True), ("c1_world", c1, cam1, False), ("rnd_world", rnd, cam2, False),
             ("rnd_compat", rnd, cam2, True), ("inst_compat", inst, cam2, True), ("inst_world", inst, cam2, False)]
+
+
+# ------------------------------------------------------------------ loader-independent readers (tests only)
+def parse_vtk_particles_py(path):
+    """A second, pure-Python reader of NetDEM's legacy-ASCII particle / wall files (POINTS + POINT_DATA arrays), written
+    from the file format alone and sharing no code with librtb200_io.so: the pin for rt_io_particles_load and the source of
+    the frames tests/test_gpu_configs.py assembles without the product loaders.  Values go text -> double -> float32, as
+    the reference's vtkDataArray::GetTuple + static_cast<float> does (src/Util/VTKReaderImpl.cpp:176-214)."""
+    tok = open(path).read().split("\n")
+    i, n, out = 0, 0, {}
+
+    def block(first, count, width):
+        vals, j = [], first
+        while len(vals) < count * width:
+            vals += tok[j].split()
+            j += 1
+        return np.array(vals[:count * width], dtype=np.float64).reshape(count, width), j
+
+    while i < len(tok):
+        w = tok[i].split()
+        if len(w) >= 3 and w[0] == "POINTS":
+            n = int(w[1])
+            out["pos"], i = block(i + 1, n, 3)
+        elif len(w) >= 3 and w[0] == "SCALARS":
+            width = int(w[3]) if len(w) > 3 else 1
+            out[w[1]], i = block(i + 2, n, width)      # skips the LOOKUP_TABLE line
+        elif len(w) >= 3 and w[0] == "VECTORS":
+            out[w[1]], i = block(i + 1, n, 3)
+        else:
+            i += 1
+    res = dict(pos=out["pos"].astype(np.float32), vel=out["vel"].astype(np.float32), quat=out["quat"].astype(np.float32),
+               id=out["id"][:, 0].astype(np.uint64), shape_id=out["shape_id"][:, 0].astype(np.uint64),
+               size=out["size"][:, 0].astype(np.float32) if "size" in out else None)
+    return res
+
+
+def parse_series_py(directory, name):
+    """.vtk.series (JSON) without the product's JSON parser: file paths and the per-file durations the frame count is
+    computed from (time[i+1] - time[i] in float32; the last file repeats the previous duration, RendererTime.cu:60-75)."""
+    d = json.load(open(os.path.join(directory, name)))
+    files = [os.path.join(directory, f["name"]) for f in d["files"]]
+    times = np.float32([f["time"] for f in d["files"]])
+    return files, times

@@ -365,3 +365,27 @@ def test_shipped_reference_files(hio):
     assert np.all((sph["face_normals"] * cen).sum(axis=1) > 0)          # outward on the tessellated sphere
     assert abs(np.linalg.norm(sph["vertices"], axis=1).max() - 0.05) < 1e-3
     assert max(len(hio.load_particles(f)["id"]) for f in s["files"][::10]) <= g["max_particle_count"]
+
+
+DATA = os.path.join(os.path.dirname(HERE), "data", "ref_files")
+
+
+@pytest.mark.skipif(not os.path.isfile(os.path.join(DATA, "config_c2.json")), reason="data/ref_files absent: run scripts/pack_ref_data.py")
+def test_particle_and_wall_loaders_equal_an_independent_parser(hio):
+    """tests/test_gpu_configs.py assembles its oracle scenes with the product's own loaders, which pins
+    driver <-> render but not the loaders.  Here every array rt_io_particles_load returns for the files that test renders
+    (particle and wall files 0 / 1, 200 / 201, 400 of BASELINE config 2, plus every 40th file) is compared bit for bit with a
+    pure-Python parser of the same text (tests/scenes.py), and the series' file list / times with json.load."""
+    import scenes
+    for name, sub in (("particle.vtk.series", "particle"), ("wall.vtk.series", "wall")):
+        s = hio.load_series(DATA + "/", name)
+        files, times = scenes.parse_series_py(DATA, name)
+        assert [os.path.normpath(f) for f in s["files"]] == [os.path.normpath(f) for f in files]
+        assert np.array_equal(np.float32(s["times"]), times)
+        for fi in sorted(set([0, 1, 200, 201, 400] + list(range(0, 401, 40)))):
+            a, b = hio.load_particles(s["files"][fi]), scenes.parse_vtk_particles_py(files[fi])
+            for k in ("pos", "vel", "quat", "id", "shape_id"):
+                assert a[k].dtype == b[k].dtype and np.array_equal(a[k], b[k]), (sub, fi, k)
+            assert (a["size"] is None) == (b["size"] is None)
+            if b["size"] is not None:
+                assert np.array_equal(a["size"], b["size"])
