@@ -7,6 +7,7 @@
 //   rtb200_render CONFIG.json [--out DIR] [--width W] [--height H] [--spp N] [--depth D] [--seed S]
 //                 [--max-files K] [--file-stride K] [--frame-stride S] [--max-frames F] [--extra-series NAME]...
 //                 [--spheres] [--drop-shape ID]... [--format pfm|exr|ppm|none] [--device N] [--quiet]
+//                 [--ranks N [--rank R]]   frame-parallel over the files: N forked processes, GPU (device + r) % count each
 //                 [--aov]     also write the first-hit albedo and normal buffers (the reference's denoiser guides,
 //                             shader/Shader.cu:270-272, src/Global/RendererImpl.cu:680-711) as <stem>_albedo / <stem>_normal
 //                             images and the primary-hit primitive ids as <stem>_primid.u32 (raw little-endian u32, row-major)
@@ -14,6 +15,9 @@
 //                             details (RT_FLAG_REF_NO_SELF_SKIP | RT_FLAG_REF_MUL_ON_RETURN): the reference's own pixels
 //                 [--fused]   the queue-free persistent path kernel (scene option fused = 1)
 #include <cuda_runtime.h>
+#include <sys/wait.h>
+#include <unistd.h>
+#include <cerrno>
 
 #include <algorithm>
 #include <atomic>
@@ -37,6 +41,7 @@ namespace {
 struct Options {
     std::string config, out = "out/", format = "pfm";
     int width = 0, height = 0, device = 0;
+    int ranks = 1, rank = -1;  // frame-parallel over the files of the series: file k of the rendered set goes to rank k % ranks
     long spp = -1, depth = -1, max_files = -1, file_stride = 1, frame_stride = 1, max_frames = -1;
     long long seed = -1;
     bool spheres = false, quiet = false, aov = false, compat = false, fused = false;
@@ -92,6 +97,8 @@ Options parse_args(int argc, char **argv) {
         else if (a == "--drop-shape") o.drop_shapes.insert((uint64_t)atoll(val()));
         else if (a == "--format") o.format = val();
         else if (a == "--device") o.device = atoi(val());
+        else if (a == "--ranks") o.ranks = std::max(1, atoi(val()));  // alone: fork one process per rank (GPU (device + r) % count)
+        else if (a == "--rank") o.rank = atoi(val());                 // with --ranks: be that rank only (external launcher)
         else if (a == "--spheres") o.spheres = true;
         else if (a == "--quiet") o.quiet = true;
         else if (a == "--aov") o.aov = true;
@@ -272,6 +279,15 @@ void add_config_spheres(rt_scene scene, const rt_io_config_view &cfg, ConfigSphe
     }
 }
 
+// Frame-parallel partition (north_star: "frame-parallel over the VTK time series"; the reference's loop over the files,
+// RendererTime.cu:420-515 / RendererMesh.cu:363-444, is serial on one GPU, docs/technical-details.md:327).  The k-th file of
+// the rendered set belongs to rank k % ranks.  A frame is a pure function of (scene of its file, sub-frame, seed, sample
+// offset = global frame index * spp), and the global index of a file's first frame follows from the durations of the
+// files before it, so every rank writes exactly the bytes the serial run writes for its files: no exchange of any kind.
+bool file_is_mine(const Options &o, size_t fi) {
+    return o.ranks <= 1 || (int)((fi / (size_t)o.file_stride) % (size_t)o.ranks) == o.rank;
+}
+
 void render_and_write(const Options &o, const rt_io_config_view &cfg, rt_scene scene, Frame &fr, const rt_camera &cam,
                       cudaStream_t st, uint32_t spp, uint32_t depth, uint64_t seed, size_t frame_total, const std::string &stem,
                       RunStats &rs) {
@@ -350,6 +366,11 @@ int run_time_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
     for (size_t fi = 0; fi < n_files; fi += (size_t)o.file_stride) {
         const float dur = rt_io_series_duration(main_ts.series, fi);
         const size_t frames = rt_io_frames_for_file(dur, cfg.fps, cfg.render_speed_ratio);
+        if (!file_is_mine(o, fi)) {  // another rank's file: only the global frame counter (sample offsets) moves on
+            frame_total += (frames + (size_t)o.frame_stride - 1) / (size_t)o.frame_stride;
+            if (o.max_frames > 0 && (long)frame_total >= o.max_frames) return 0;
+            continue;
+        }
         // ---- scene of this file (the reference switches to this file's IAS + SBT, RendererTime.cu:420-424)
         RT(rt_scene_clear_geometry(scene));
         add_config_spheres(scene, cfg, cs);
@@ -455,6 +476,11 @@ int run_mesh_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
         const rt_io_mesh_view &mv = views[fi];
         const float dur = rt_io_series_duration(series, fi);
         const size_t frames = rt_io_frames_for_file(dur, cfg.fps, cfg.render_speed_ratio);
+        if (!file_is_mine(o, fi)) {
+            frame_total += (frames + (size_t)o.frame_stride - 1) / (size_t)o.frame_stride;
+            if (o.max_frames > 0 && (long)frame_total >= o.max_frames) return 0;
+            continue;
+        }
         const size_t nv = mv.n_particles ? mv.vertex_offset[mv.n_particles] : 0;
         if (nv > cap) {
             if (d_v) CU(cudaFree(d_v));
@@ -494,7 +520,38 @@ int run_mesh_mode(const Options &o, const rt_io_config_view &cfg, rt_scene scene
 }  // namespace
 
 int main(int argc, char **argv) {
-    const Options o = parse_args(argc, argv);
+    Options o = parse_args(argc, argv);
+    if (o.ranks > 1 && o.rank >= o.ranks) die(1, "--rank %d outside --ranks %d", o.rank, o.ranks);
+    if (o.ranks > 1 && o.rank < 0) {
+        // one child process per rank, forked before this process has touched CUDA; the parent only waits
+        std::vector<pid_t> kids;
+        for (int r = 0; r < o.ranks; r++) {
+            fflush(stdout);
+            fflush(stderr);
+            const pid_t pid = fork();
+            if (pid < 0) die(5, "fork: %s", strerror(errno));
+            if (pid == 0) {
+                o.rank = r;
+                kids.clear();
+                break;
+            }
+            kids.push_back(pid);
+        }
+        if (o.rank < 0) {
+            int failed = 0;
+            for (pid_t pid : kids) {
+                int status = 0;
+                if (waitpid(pid, &status, 0) < 0 || !WIFEXITED(status) || WEXITSTATUS(status) != 0) failed++;
+            }
+            printf("{\"ranks\": %d, \"failed\": %d, \"partition\": \"frame-parallel: file k of the rendered set -> rank k %% ranks\"}\n", o.ranks, failed);
+            return failed ? 6 : 0;
+        }
+        int n_dev = 0;
+        CU(cudaGetDeviceCount(&n_dev));
+        if (n_dev < 1) die(3, "no CUDA device");
+        o.device = (o.device + o.rank) % n_dev;  // fewer GPUs than ranks: ranks share devices
+    }
+    if (o.rank < 0) o.rank = 0;
     rt_io_config cfgh = nullptr;
     if (int rc = rt_io_config_load(o.config.c_str(), &cfgh)) die(-2 & 0xFF, "config: %s (code %d)", rt_io_last_error(), rc);
     rt_io_config_view cfg;
@@ -539,10 +596,10 @@ int main(int argc, char **argv) {
     const double loop_s = std::max(wall - rs.load_s, 1e-9);
     printf("{\"frames\": %zu, \"width\": %u, \"height\": %u, \"segments\": %llu, \"prims\": %llu, \"build_ms\": %.3f, \"render_ms\": %.3f, "
            "\"wall_s\": %.3f, \"load_s\": %.3f, \"loop_s\": %.3f, \"frames_per_s\": %.3f, \"mrays_per_s\": %.2f, "
-           "\"mrays_per_s_render\": %.2f, \"build_mprims_per_s\": %.2f, \"mode\": \"%s\"}\n",
+           "\"mrays_per_s_render\": %.2f, \"build_mprims_per_s\": %.2f, \"mode\": \"%s\", \"rank\": %d, \"ranks\": %d, \"device\": %d}\n",
            rs.frames, fr.w, fr.h, rs.segments, rs.prims, rs.build_ms, rs.render_ms, wall, rs.load_s, loop_s, rs.frames / loop_s,
            rs.segments / loop_s * 1e-6, rs.render_ms > 0 ? rs.segments / rs.render_ms * 1e-3 : 0.0,
-           rs.build_ms > 0 ? rs.prims / rs.build_ms * 1e-3 : 0.0, cfg.mesh ? "mesh" : "time");
+           rs.build_ms > 0 ? rs.prims / rs.build_ms * 1e-3 : 0.0, cfg.mesh ? "mesh" : "time", o.rank, o.ranks, o.device);
     RT(rt_scene_destroy(scene));
     rt_context_destroy(g_ctx);
     return rc;

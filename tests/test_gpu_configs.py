@@ -86,8 +86,11 @@ def test_c2_time_series_with_walls_matches_oracle(tmp_path, pkg, hio, oracle):
         gs = [sd.add_triangles(sh["vertices"], sh["vertex_normals"]) for sh in shapes]
         n_inst = 0
         for sr in series:
-            p = hio.load_particles(sr["files"][fi])
-            nxt = hio.load_particles(sr["files"][min(fi + 1, 400)])
+            # file 0 of both series comes from the pure-Python parser of tests/scenes.py, not from the product loaders
+            # (tests/test_io.py pins the loaders against the same parser on every file used here)
+            rd = scenes.parse_vtk_particles_py if fi == 0 else hio.load_particles
+            p = rd(sr["files"][fi])
+            nxt = rd(sr["files"][min(fi + 1, 400)])
             for k in range(len(p["id"])):
                 if int(p["shape_id"][k]) == 2:
                     continue

@@ -182,3 +182,36 @@ def test_mesh_mode_driver_cache_then_render(tmp_path, pkg, hio, oracle):
             want = (o["accum"][:, :3] * np.float32(1.0 / SPP)).reshape(H, W, 3)
             assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (fi, f)
             ft += 1
+
+
+def _dir_bytes(path):
+    return {f: open(os.path.join(path, f), "rb").read() for f in sorted(os.listdir(path))}
+
+
+def test_frame_parallel_ranks_write_the_serial_runs_bytes(tmp_path, pkg, hio):
+    """rtb200_render --ranks N: the files of the series are dealt to N forked processes (file k -> rank k % N, one GPU each, or
+    a shared GPU when the box has fewer).  Every output file must be byte-identical to the serial run's (frame-
+    parallel output files must be byte-identical to the serial run) — sample offsets follow the global frame index, which a
+    rank derives from the durations of the files it skips.  Also through --rank R with an external launcher."""
+    d = str(tmp_path) + "/"
+    make_time_inputs(d)
+    json.dump(config_for(d, False, "t.vtk.series"), open(d + "config.json", "w"))
+    serial = run_driver(d + "config.json", d + "out1", "--frame-stride", "4")
+    assert serial["frames"] == 6 and serial["ranks"] == 1
+    want = _dir_bytes(d + "out1")
+    assert len(want) == 6
+    # forked by the driver itself: one summary line per rank, then the parent's
+    cmd = [DRIVER, d + "config.json", "--out", d + "out2", "--width", str(W), "--height", str(H), "--spp", str(SPP), "--depth", str(DEPTH),
+           "--seed", str(SEED), "--format", "pfm", "--quiet", "--frame-stride", "4", "--ranks", "2"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [json.loads(x) for x in r.stdout.strip().splitlines()]
+    assert lines[-1]["ranks"] == 2 and lines[-1]["failed"] == 0
+    per_rank = sorted((x["rank"], x["frames"]) for x in lines[:-1])
+    assert per_rank == [(0, 3), (1, 3)]
+    assert _dir_bytes(d + "out2") == want
+    # three ranks for two files (one rank idles), launched one by one as an external launcher would
+    for rk in range(3):
+        s = run_driver(d + "config.json", d + "out3", "--frame-stride", "4", "--ranks", "3", "--rank", str(rk))
+        assert s["rank"] == rk and s["frames"] == (3 if rk < 2 else 0)
+    assert _dir_bytes(d + "out3") == want
